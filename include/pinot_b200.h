@@ -1,0 +1,162 @@
+/*
+ * pinot_b200 -- C-ABI of the B200 (sm_100a) kernels behind pinot's
+ * graph-convolution -> Gaussian-process hot path.
+ *
+ * Conventions:
+ *   - every pointer is a DEVICE pointer unless stated otherwise; matrices are row-major fp32 with an
+ *     explicit leading dimension (in elements); CSR indices are int32;
+ *   - every entry point is asynchronous on `stream`, returns 0 on success and a non-zero code
+ *     (1 bad argument, 2 CUDA error, 3 documented limit exceeded) otherwise; the message is
+ *     available from pinot_b200_last_error() (thread-local);
+ *   - the library never allocates or frees device memory and never takes ownership: outputs and
+ *     scratch are provided by the caller (see the *_workspace_bytes queries).
+ *
+ * The reference (choderalab/pinot) is pure Python; the "reference interface each entry point
+ * replaces" is therefore the torch / DGL call made at the cited pinot file:line.
+ */
+#ifndef PINOT_B200_H_
+#define PINOT_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifndef __DRIVER_TYPES_H__
+typedef struct CUstream_st* cudaStream_t;
+#endif
+
+#if defined(__GNUC__)
+#define PINOT_B200_API __attribute__((visibility("default")))
+#else
+#define PINOT_B200_API
+#endif
+
+/* Last error message of the calling thread ("" if none). */
+PINOT_B200_API const char* pinot_b200_last_error(void);
+/* ABI version of this header (bumped on any signature change). */
+PINOT_B200_API int pinot_b200_abi_version(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * Kernel (1): message passing.
+ * out[i,:] = dst_scale[i] * sum_{e in [indptr[i],indptr[i+1])} src_scale[indices[e]] * x[indices[e],:]
+ * (either scale pointer may be NULL = 1).  CSR is sorted by destination node.
+ * Replaces dgl.nn.pytorch.conv.GraphConv(norm="both") / SAGEConv("mean")'s
+ * update_all(copy_src, sum|mean) reached from pinot/representation/dgl_legacy.py:40-50
+ * (GraphConv: src_scale = out_deg^-1/2, dst_scale = in_deg^-1/2, degrees clamped to >= 1;
+ *  SAGEConv mean: src_scale = NULL, dst_scale = 1/max(in_deg,1)).
+ * --------------------------------------------------------------------------------------------- */
+PINOT_B200_API int pinot_b200_mp_csr_aggregate_fwd(const float* x, float* out, const int32_t* indptr,
+                                    const int32_t* indices, const float* src_scale,
+                                    const float* dst_scale, int64_t n_dst, int64_t feat,
+                                    cudaStream_t stream);
+/* Gradient of the above w.r.t. x: dx[j,:] = src_scale[j] * sum_{i: j->i} dst_scale[i] * dout[i,:].
+ * indptr_t / indices_t is the CSR of the TRANSPOSED graph (sorted by source node).  Replaces the
+ * autograd of DGL's SpMM (same call sites). */
+PINOT_B200_API int pinot_b200_mp_csr_aggregate_bwd(const float* dout, float* dx, const int32_t* indptr_t,
+                                    const int32_t* indices_t, const float* src_scale,
+                                    const float* dst_scale, int64_t n_src, int64_t feat,
+                                    cudaStream_t stream);
+
+/* Readout: out[g,:] = sum (or mean) of x[n,:] over the nodes n in [offsets[g], offsets[g+1]).
+ * Replaces dgl.sum_nodes(g, "h") at pinot/representation/sequential.py:78,92-103. */
+PINOT_B200_API int pinot_b200_segment_readout_fwd(const float* x, float* out, const int32_t* offsets,
+                                   int64_t n_seg, int64_t feat, int mean, cudaStream_t stream);
+/* dx[n,:] = dout[node_seg[n],:] (divided by the segment size for mean). */
+PINOT_B200_API int pinot_b200_segment_readout_bwd(const float* dout, float* dx, const int32_t* offsets,
+                                   const int32_t* node_seg, int64_t n_nodes, int64_t feat, int mean,
+                                   cudaStream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Kernel (2): node update  y = act(x W + b)  (act: 0 none, 1 tanh).
+ * w_is_out_in = 1: W is a torch.nn.Linear weight (out, in)  -- Sequential.f_in,
+ *                  pinot/representation/sequential.py:41-43,84, and SAGEConv fc_self / fc_neigh;
+ * w_is_out_in = 0: W is a DGL GraphConv weight (in, out)    -- pinot/representation/dgl_legacy.py:40.
+ * accumulate = 1 adds the product to the existing contents of y before bias/activation.
+ * --------------------------------------------------------------------------------------------- */
+PINOT_B200_API int pinot_b200_node_update_fwd(const float* x, const float* w, const float* bias, float* y,
+                               int64_t n_rows, int64_t in_feats, int64_t out_feats, int w_is_out_in,
+                               int act, int accumulate, cudaStream_t stream);
+/* Backward: dz = dy * act'(y); dx = dz W^T; dw = x^T dz (in W's layout); db = colsum(dz).
+ * dz_scratch (n_rows x out_feats) is required when act != 0; dx / dw / db may be NULL. */
+PINOT_B200_API int pinot_b200_node_update_bwd(const float* dy, const float* y, const float* x, const float* w,
+                               float* dz_scratch, float* dx, float* dw, float* db, int64_t n_rows,
+                               int64_t in_feats, int64_t out_feats, int w_is_out_in, int act,
+                               cudaStream_t stream);
+
+/* General row-major fp32 GEMM  C = alpha op(A) op(B) + beta C  (transX != 0: X is stored transposed).
+ * Replaces torch.matmul / `@` in pinot/regressors/gaussian_process_regressor.py:212,218,392-414. */
+PINOT_B200_API int pinot_b200_sgemm(int transA, int transB, int64_t M, int64_t N, int64_t K, float alpha,
+                     const float* A, int64_t lda, const float* B, int64_t ldb, float beta, float* C,
+                     int64_t ldc, cudaStream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Kernel (3): Gram matrix.  kind 0 = RBF (pinot/regressors/kernels/rbf.py:31-55: exp(variance) *
+ * exp(-0.5 * ||(x - x') * exp(scale)||_2)), kind 1 = Matern-5/2 (pinot/regressors/kernels/matern.py:30-63).
+ * scale has scale_len = d (ARD) or 1 entries; variance is a device scalar.
+ * out[i,j] = K(x_i, y_j) + (i == j) * (diag_add + (diag_add_log ? exp(*diag_add_log) : 0)):
+ * the fused `_perturb` (gaussian_process_regressor.py:29-46, rectangular matrices included) and
+ * noise term exp(log_sigma) * I (:103-105).
+ * --------------------------------------------------------------------------------------------- */
+PINOT_B200_API int pinot_b200_gram_fwd(int kind, const float* x, const float* y, const float* scale,
+                        int64_t scale_len, const float* variance, float* out, int64_t ldo, int64_t n,
+                        int64_t n2, int64_t d, float diag_add, const float* diag_add_log,
+                        cudaStream_t stream);
+/* Backward of the Gram matrix given dk = dLoss/dK (n x n2).  Outputs (any may be NULL, all are
+ * overwritten): dx (n x d), dy (n2 x d), dscale (scale_len), dvariance (1).  symmetric = 1 promises
+ * x == y and dk == dk^T: only the row-side pass runs and the caller doubles dx and dscale.
+ * Replaces autograd through torch.norm / exp at kernels/rbf.py:31-53 (sub-gradient 0 at d = 0).
+ * Limit: d <= 256. */
+PINOT_B200_API int pinot_b200_gram_bwd(int kind, const float* x, const float* y, const float* scale,
+                        int64_t scale_len, const float* variance, const float* dk, int64_t ldk,
+                        int64_t n, int64_t n2, int64_t d, float* dx, float* dy, float* dscale,
+                        float* dvariance, int symmetric, cudaStream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Kernel (4): blocked Cholesky sweep over the stacked matrix e = [A ; X], (n + r) x n, ld >= n:
+ *   A (n x n; lower triangle read)  -> L, A = L L^T (strict upper triangle left untouched)
+ *   X (r x n)                       -> X L^{-T}
+ * r = n_ext_dense (+ n if ext_identity: the caller stores I in those rows and gets L^{-T} back;
+ * they must FOLLOW the dense rows).  diag_out (n, optional) receives diag(L).  *info (device int)
+ * is 0 on success or 1 + the first non-positive pivot (LAPACK convention).  workspace must hold
+ * pinot_b200_potrf_workspace_bytes(n) bytes.
+ * Replaces torch.cholesky + torch.triangular_solve at gaussian_process_regressor.py:108-119,215,373-390.
+ * --------------------------------------------------------------------------------------------- */
+PINOT_B200_API int64_t pinot_b200_potrf_workspace_bytes(int64_t n);
+PINOT_B200_API int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, int ext_identity,
+                         float* diag_out, void* workspace, int* info, cudaStream_t stream);
+/* X (r x n) <- X L^{-T} for an already factored lower-triangular L (torch.triangular_solve(
+ * input=X^T, A=L, upper=False) transposed; gaussian_process_regressor.py:112-114,215,376-390). */
+PINOT_B200_API int pinot_b200_trsm_rlt(const float* l, int64_t ldl, int64_t n, float* x, int64_t ldx, int64_t r,
+                        cudaStream_t stream);
+/* Zero the strict upper triangle of an n x n matrix (torch.cholesky's output convention). */
+PINOT_B200_API int pinot_b200_zero_upper(float* a, int64_t ld, int64_t n, cudaStream_t stream);
+/* y[i] = sum_k m[i,k] v[k] (upper != 0: only k >= i), one warp per row.  alpha = L^{-T} z
+ * (gaussian_process_regressor.py:117-119) and small matrix-vector products. */
+PINOT_B200_API int pinot_b200_gemv_rows(const float* m, int64_t ld, int64_t rows, int64_t cols, int upper,
+                         const float* v, float* y, cudaStream_t stream);
+/* out3[0] = 0.5 z.z + trace(L) + 0.5 n log(2 pi)   (pinot's objective, gaussian_process_regressor.py:160-164)
+ * out3[1] = 0.5 z.z + sum_i log L_ii + 0.5 n log(2 pi)   (exact negative log marginal likelihood)
+ * out3[2] = z.z                          with z = L^{-1} y, diag_l = diag(L). */
+PINOT_B200_API int pinot_b200_gp_nll(const float* diag_l, const float* z, int64_t n, float* out3,
+                      cudaStream_t stream);
+/* Closed-form gradient of the objective w.r.t. K (full symmetric n x n, scaled by *upstream if
+ * given): 0.5 L^{-T} diag(L) L^{-1} - 0.5 alpha alpha^T   (exact_logdet = 0, trace(L) objective)
+ *         0.5 K^{-1}                 - 0.5 alpha alpha^T   (exact_logdet = 1).
+ * linv_t = L^{-T} (upper triangular, from the identity extension rows of the sweep).
+ * Replaces autograd's cholesky_backward / triangular_solve_backward for :123-166. */
+PINOT_B200_API int pinot_b200_gp_nll_grad(const float* linv_t, int64_t ld, int64_t n, const float* diag_l,
+                           const float* alpha, const float* upstream, int exact_logdet, float* dk,
+                           int64_t lddk, cudaStream_t stream);
+/* Predictive marginals from vt = K_te,tr L^{-T} (n_te x n) and z = L^{-1} y:
+ * mean[i] = vt[i,:].z ; var[i] = exp(*variance) + eps - |vt[i,:]|^2  (var may be NULL).
+ * Equals the mean and the diagonal of the covariance at gaussian_process_regressor.py:212-221. */
+PINOT_B200_API int pinot_b200_gp_predict_mean_var(const float* vt, int64_t ld, int64_t n_te, int64_t n,
+                                   const float* z, const float* variance, float eps, float* mean,
+                                   float* var, cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PINOT_B200_H_ */

@@ -1,0 +1,402 @@
+// Kernel (4): blocked right-looking Cholesky "sweep" over an augmented matrix, plus the small
+// kernels that turn its outputs into the exact-GP loss, its closed-form gradient and the
+// predictive mean / variance.  Replaces torch.cholesky + torch.triangular_solve (cuSOLVER potrf,
+// cuBLAS trsm) and autograd's cholesky_backward on the path
+// pinot/regressors/gaussian_process_regressor.py:85-121 (factor + alpha), :123-166 (loss),
+// :168-233 (condition).
+//
+// One sweep factors the stacked matrix E = [ A ; X ] ((n + r) x n, row-major):
+//     A (n x n, lower triangle used)  ->  L            with  A = L L^T
+//     X (r x n, "extension rows")     ->  X L^{-T}
+// because the panel TRSM and the trailing rank-nb update treat the extension rows exactly like
+// the rows of A below the panel.  With X = [ y^T ; I ] the sweep yields z^T = (L^{-1} y)^T and
+// L^{-T} (all that loss + gradient need); with X = [ y^T ; K_te,tr ] it yields z and
+// V^T = K_te,tr L^{-T} (all that the predictive distribution needs).  Identity extension rows are
+// only touched from the column block where their 1 sits, so L^{-T} costs n^3/3 extra flops.
+#include "gemm.cuh"
+#include "../../include/pinot_b200.h"
+#include <math.h>
+
+namespace {
+
+constexpr int NB = 64;        // panel width
+constexpr int LDL = NB + 4;   // shared stride of the diagonal block
+constexpr int PR = 256;       // panel rows per CTA (one thread per row)
+constexpr int LDT = NB + 1;   // shared stride of the staged panel rows
+
+// Factor the nb x nb diagonal block held (unfactored, lower part valid) in Ls.  On exit the lower
+// triangle of Ls holds L11 and invd[j] = 1 / L11[j][j].  Returns the first failing pivot (0-based)
+// or -1.  All 256 threads take part.
+__device__ int factor_diag_block(float* __restrict__ Ls, float* __restrict__ dj, int nb) {
+    const int tid = threadIdx.x;
+    const int ti = tid >> 4, tc = tid & 15;
+    int fail = -1;
+    for (int j = 0; j < nb; ++j) {
+        __syncthreads();
+        float d = Ls[j * LDL + j];
+        if (!(d > 0.f)) {  // also catches NaN
+            if (fail < 0) fail = j;
+            d = 1.f;
+        }
+        if (tid == 0) dj[j] = d;
+        const float inv = 1.f / d;
+        for (int i = j + 1 + ti; i < nb; i += 16) {
+            const float lij = Ls[i * LDL + j] * inv;
+            for (int c = j + 1 + tc; c <= i; c += 16) Ls[i * LDL + c] = fmaf(-lij, Ls[c * LDL + j], Ls[i * LDL + c]);
+        }
+    }
+    __syncthreads();
+    // L[j][j] = sqrt(d_j); dj[j] <- 1 / L[j][j]; then scale the columns: L[i][j] = S[i][j] / L[j][j]
+    if (tid < nb) {
+        const float l = sqrtf(dj[tid]);
+        Ls[tid * LDL + tid] = l;
+        dj[tid] = 1.f / l;
+    }
+    __syncthreads();
+    for (int idx = tid; idx < nb * nb; idx += blockDim.x) {
+        const int i = idx / nb, j = idx - i * nb;
+        if (j < i) Ls[i * LDL + j] *= dj[j];
+    }
+    __syncthreads();
+    return fail;
+}
+
+// Panel step of the sweep for column block [c0, c0+nb):
+//   * every CTA loads the diagonal block (from `D`, leading dimension ldd) and, unless it is
+//     already factored, factors it in shared memory; CTA 0 stores L11 into `wdiag` (the deferred
+//     diagonal write-back keeps late CTAs from reading a half-written block);
+//   * each CTA then solves X <- X L11^{-T} for its PR rows of the panel (rows [row_beg,row_end)
+//     of `P`, leading dimension ldp, columns [c0, c0+nb)).
+__global__ void __launch_bounds__(PR)
+chol_panel_kernel(const float* __restrict__ D, int64_t ldd, float* __restrict__ P, int64_t ldp,
+                  int c0, int nb, int64_t row_beg, int64_t row_end, int factored,
+                  float* __restrict__ wdiag, int* __restrict__ info) {
+    extern __shared__ __align__(16) float smem[];
+    float* Ls = smem;                 // [NB][LDL]
+    float* dj = Ls + NB * LDL;        // [NB]
+    float* Ts = dj + NB;              // [PR][LDT]
+    const int tid = threadIdx.x;
+
+    for (int idx = tid; idx < NB * NB; idx += blockDim.x) {
+        const int i = idx >> 6, j = idx & 63;
+        float v = (i == j) ? 1.f : 0.f;
+        if (i < nb && j <= i) v = __ldg(D + (int64_t)(c0 + i) * ldd + c0 + j);
+        Ls[i * LDL + j] = v;
+    }
+    for (int i = tid; i < NB; i += blockDim.x) dj[i] = 1.f;
+    __syncthreads();
+    if (!factored) {
+        const int fail = factor_diag_block(Ls, dj, nb);
+        if (blockIdx.x == 0) {
+            if (fail >= 0 && tid == 0) atomicCAS(info, 0, c0 + fail + 1);
+            for (int idx = tid; idx < NB * NB; idx += blockDim.x) {
+                const int i = idx >> 6, j = idx & 63;
+                wdiag[idx] = (j <= i) ? Ls[i * LDL + j] : 0.f;
+            }
+        }
+    } else {
+        if (tid < nb) dj[tid] = 1.f / Ls[tid * LDL + tid];
+        __syncthreads();
+    }
+
+    const int64_t r0 = row_beg + (int64_t)blockIdx.x * PR;
+    if (r0 >= row_end) return;
+    const int rows_here = (int)min((int64_t)PR, row_end - r0);
+    const bool vec = ((ldp & 3) == 0) && ((reinterpret_cast<uintptr_t>(P) & 15u) == 0) && ((c0 & 3) == 0);
+
+    // stage rows (coalesced) -> Ts
+    for (int idx = tid; idx < PR * (NB / 4); idx += blockDim.x) {
+        const int r = idx >> 4, q = (idx & 15) * 4;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r < rows_here) {
+            const float* src = P + (r0 + r) * ldp + c0 + q;
+            if (vec && q + 3 < nb) {
+                v = *reinterpret_cast<const float4*>(src);
+            } else {
+                if (q + 0 < nb) v.x = src[0];
+                if (q + 1 < nb) v.y = src[1];
+                if (q + 2 < nb) v.z = src[2];
+                if (q + 3 < nb) v.w = src[3];
+            }
+        }
+        Ts[r * LDT + q + 0] = v.x;
+        Ts[r * LDT + q + 1] = v.y;
+        Ts[r * LDT + q + 2] = v.z;
+        Ts[r * LDT + q + 3] = v.w;
+    }
+    __syncthreads();
+
+    // forward substitution, one row per thread, the row lives in registers
+    float xr[NB];
+#pragma unroll
+    for (int j = 0; j < NB; ++j) xr[j] = Ts[tid * LDT + j];
+#pragma unroll
+    for (int j = 0; j < NB; ++j) {
+        float s0 = xr[j], s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+        for (int t = 0; t < j; ++t) {
+            const float l = Ls[j * LDL + t];
+            if ((t & 3) == 0) s0 = fmaf(-xr[t], l, s0);
+            else if ((t & 3) == 1) s1 = fmaf(-xr[t], l, s1);
+            else if ((t & 3) == 2) s2 = fmaf(-xr[t], l, s2);
+            else s3 = fmaf(-xr[t], l, s3);
+        }
+        xr[j] = ((s0 + s1) + (s2 + s3)) * dj[j];
+    }
+#pragma unroll
+    for (int j = 0; j < NB; ++j) Ts[tid * LDT + j] = xr[j];
+    __syncthreads();
+
+    for (int idx = tid; idx < PR * (NB / 4); idx += blockDim.x) {
+        const int r = idx >> 4, q = (idx & 15) * 4;
+        if (r >= rows_here) continue;
+        float* dst = P + (r0 + r) * ldp + c0 + q;
+        const float4 v = make_float4(Ts[r * LDT + q], Ts[r * LDT + q + 1], Ts[r * LDT + q + 2], Ts[r * LDT + q + 3]);
+        if (vec && q + 3 < nb) {
+            *reinterpret_cast<float4*>(dst) = v;
+        } else {
+            if (q + 0 < nb) dst[0] = v.x;
+            if (q + 1 < nb) dst[1] = v.y;
+            if (q + 2 < nb) dst[2] = v.z;
+            if (q + 3 < nb) dst[3] = v.w;
+        }
+    }
+}
+
+// Deferred write-back of the factored diagonal blocks, optional zeroing of the strict upper
+// triangle of the n x n block (torch.cholesky returns zeros there), and extraction of diag(L).
+__global__ void __launch_bounds__(256)
+chol_writeback_kernel(float* __restrict__ E, int64_t ld, int n, const float* __restrict__ wdiag,
+                      float* __restrict__ diag_out) {
+    const int b = blockIdx.x, c0 = b * NB;
+    const int nb = min(NB, n - c0);
+    const float* W = wdiag + (size_t)b * NB * NB;
+    for (int idx = threadIdx.x; idx < NB * NB; idx += blockDim.x) {
+        const int i = idx >> 6, j = idx & 63;
+        if (i < nb && j <= i) {
+            const float v = W[idx];
+            E[(int64_t)(c0 + i) * ld + c0 + j] = v;
+            if (i == j && diag_out) diag_out[c0 + i] = v;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+zero_upper_kernel(float* __restrict__ A, int64_t ld, int64_t n) {
+    for (int64_t i = blockIdx.y; i < n; i += gridDim.y)
+        for (int64_t j = i + 1 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n;
+             j += (int64_t)gridDim.x * blockDim.x)
+            A[i * ld + j] = 0.f;
+}
+
+__device__ __forceinline__ float block_sum(float v, float* red) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    float s = 0.f;
+    const int nw = (blockDim.x + 31) >> 5;
+    for (int w = 0; w < nw; ++w) s += red[w];
+    return s;
+}
+
+// out[0] = 0.5 z.z + trace(L) + 0.5 n log(2 pi)        (the reference's objective, :160-164)
+// out[1] = 0.5 z.z + sum log L_ii + 0.5 n log(2 pi)    (the exact negative log marginal likelihood)
+// out[2] = z.z
+__global__ void __launch_bounds__(1024)
+gp_nll_kernel(const float* __restrict__ diagL, const float* __restrict__ z, int n, float* __restrict__ out) {
+    __shared__ float red[32];
+    float tr = 0.f, ld = 0.f, q = 0.f;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const float l = diagL[i];
+        tr += l;
+        ld += logf(l);
+        const float zi = z[i];
+        q = fmaf(zi, zi, q);
+    }
+    tr = block_sum(tr, red);
+    ld = block_sum(ld, red);
+    q = block_sum(q, red);
+    if (threadIdx.x == 0) {
+        const float c = 0.5f * (float)n * 1.8378770664093453f;  // log(2 pi)
+        out[0] = 0.5f * q + tr + c;
+        out[1] = 0.5f * q + ld + c;
+        out[2] = q;
+    }
+}
+
+// y[i] = sum_{k >= (upper ? i : 0)} M[i][k] * v[k]; one warp per row.
+__global__ void __launch_bounds__(256)
+gemv_rows_kernel(const float* __restrict__ M, int64_t ld, int64_t rows, int64_t cols, int upper,
+                 const float* __restrict__ v, float* __restrict__ y) {
+    const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int lane = threadIdx.x & 31;
+    const int64_t kb = upper ? (row & ~(int64_t)31) : 0;
+    float s = 0.f;
+    for (int64_t k = kb + lane; k < cols; k += 32) {
+        if (!upper || k >= row) s = fmaf(__ldg(M + row * ld + k), __ldg(v + k), s);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) y[row] = s;
+}
+
+// mean[i] = Vt[i,:] . z ; var[i] = kdiag - |Vt[i,:]|^2 ; one warp per test point.
+__global__ void __launch_bounds__(256)
+gp_predict_kernel(const float* __restrict__ Vt, int64_t ld, int64_t n_te, int64_t n, const float* __restrict__ z,
+                  const float* __restrict__ variance, float eps, float* __restrict__ mean, float* __restrict__ var) {
+    const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= n_te) return;
+    const int lane = threadIdx.x & 31;
+    float m = 0.f, q = 0.f;
+    for (int64_t k = lane; k < n; k += 32) {
+        const float v = __ldg(Vt + row * ld + k);
+        m = fmaf(v, __ldg(z + k), m);
+        q = fmaf(v, v, q);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        m += __shfl_xor_sync(0xffffffffu, m, o);
+        q += __shfl_xor_sync(0xffffffffu, q, o);
+    }
+    if (lane == 0) {
+        mean[row] = m;
+        if (var) var[row] = expf(__ldg(variance)) + eps - q;
+    }
+}
+
+size_t panel_smem_bytes() { return sizeof(float) * (size_t)(NB * LDL + NB + PR * LDT); }
+
+int launch_panel(const float* D, int64_t ldd, float* P, int64_t ldp, int c0, int nb, int64_t row_beg,
+                 int64_t row_end, int factored, float* wdiag, int* info, cudaStream_t stream) {
+    const size_t smem = panel_smem_bytes();
+    PB_CUDA(cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t nblk = pb::ceil_div(row_end > row_beg ? row_end - row_beg : 0, PR);
+    if (nblk < 1) nblk = 1;
+    chol_panel_kernel<<<(unsigned)nblk, PR, smem, stream>>>(D, ldd, P, ldp, c0, nb, row_beg, row_end, factored,
+                                                            wdiag, info);
+    return pb::check_launch("chol_panel");
+}
+
+}  // namespace
+
+extern "C" {
+
+int64_t pinot_b200_potrf_workspace_bytes(int64_t n) {
+    if (n < 0) return -1;
+    return (int64_t)sizeof(float) * pb::ceil_div(n, NB) * NB * NB;
+}
+
+int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, int ext_identity,
+                         float* diag_out, void* workspace, int* info, cudaStream_t stream) {
+    PB_REQUIRE(n >= 0 && n < (1ll << 30) && n_ext_dense >= 0 && ld >= n, "potrf_ext: invalid sizes");
+    PB_REQUIRE(info, "potrf_ext: info pointer is required");
+    PB_CUDA(cudaMemsetAsync(info, 0, sizeof(int), stream));
+    if (n == 0) return pb::PB_OK;
+    PB_REQUIRE(e && workspace, "potrf_ext: null pointer");
+    float* wdiag = static_cast<float*>(workspace);
+    const int64_t r_total = n_ext_dense + (ext_identity ? n : 0);
+    for (int64_t c0 = 0; c0 < n; c0 += NB) {
+        const int nb = (int)((n - c0) < NB ? (n - c0) : NB);
+        const int64_t c1 = c0 + nb;
+        const int64_t r_act = ext_identity ? (n_ext_dense + c1) : r_total;
+        const int64_t row_beg = c1, row_end = n + r_act;
+        int rc = launch_panel(e, ld, e, ld, (int)c0, nb, row_beg, row_end, 0, wdiag + (c0 / NB) * NB * NB, info, stream);
+        if (rc) return rc;
+        if (c1 < n) {
+            pb::GemmParams g;
+            g.M = (int)(row_end - c1); g.N = (int)(n - c1); g.K = nb;
+            g.A = e + c1 * ld + c0; g.lda = ld; g.transA = false;
+            g.B = e + c1 * ld + c0; g.ldb = ld; g.transB = true;
+            g.C = e + c1 * ld + c1; g.ldc = ld;
+            g.alpha = -1.f; g.beta = 1.f; g.lower = 1;
+            rc = pb::gemm(g, stream);
+            if (rc) return rc;
+        }
+    }
+    chol_writeback_kernel<<<(unsigned)pb::ceil_div(n, NB), 256, 0, stream>>>(e, ld, (int)n, wdiag, diag_out);
+    return pb::check_launch("chol_writeback");
+}
+
+int pinot_b200_trsm_rlt(const float* l, int64_t ldl, int64_t n, float* x, int64_t ldx, int64_t r,
+                        cudaStream_t stream) {
+    // X (r x n) <- X L^{-T}, i.e. X^T <- L^{-1} X^T, with L already factored (lower, n x n).
+    PB_REQUIRE(n >= 0 && r >= 0 && ldl >= n && ldx >= n && n < (1ll << 30), "trsm_rlt: invalid sizes");
+    if (n == 0 || r == 0) return pb::PB_OK;
+    PB_REQUIRE(l && x, "trsm_rlt: null pointer");
+    for (int64_t c0 = 0; c0 < n; c0 += NB) {
+        const int nb = (int)((n - c0) < NB ? (n - c0) : NB);
+        const int64_t c1 = c0 + nb;
+        int rc = launch_panel(l, ldl, x, ldx, (int)c0, nb, 0, r, 1, nullptr, nullptr, stream);
+        if (rc) return rc;
+        if (c1 < n) {
+            pb::GemmParams g;
+            g.M = (int)r; g.N = (int)(n - c1); g.K = nb;
+            g.A = x + c0; g.lda = ldx; g.transA = false;
+            g.B = l + c1 * ldl + c0; g.ldb = ldl; g.transB = true;
+            g.C = x + c1; g.ldc = ldx; g.alpha = -1.f; g.beta = 1.f;
+            rc = pb::gemm(g, stream);
+            if (rc) return rc;
+        }
+    }
+    return pb::PB_OK;
+}
+
+int pinot_b200_zero_upper(float* a, int64_t ld, int64_t n, cudaStream_t stream) {
+    PB_REQUIRE(n >= 0 && ld >= n, "zero_upper: invalid sizes");
+    if (n <= 1) return pb::PB_OK;
+    PB_REQUIRE(a, "zero_upper: null pointer");
+    const int64_t gx = pb::ceil_div(n, 256) < 64 ? pb::ceil_div(n, 256) : 64;
+    dim3 grid((unsigned)gx, (unsigned)(n < 65535 ? n : 65535));
+    zero_upper_kernel<<<grid, 256, 0, stream>>>(a, ld, n);
+    return pb::check_launch("zero_upper");
+}
+
+int pinot_b200_gp_nll(const float* diag_l, const float* z, int64_t n, float* out3, cudaStream_t stream) {
+    PB_REQUIRE(n >= 0 && n < (1ll << 31) && out3 && (n == 0 || (diag_l && z)), "gp_nll: invalid arguments");
+    gp_nll_kernel<<<1, 1024, 0, stream>>>(diag_l, z, (int)n, out3);
+    return pb::check_launch("gp_nll");
+}
+
+int pinot_b200_gemv_rows(const float* m, int64_t ld, int64_t rows, int64_t cols, int upper,
+                         const float* v, float* y, cudaStream_t stream) {
+    PB_REQUIRE(rows >= 0 && cols >= 0 && ld >= cols, "gemv_rows: invalid sizes");
+    if (rows == 0) return pb::PB_OK;
+    PB_REQUIRE(m && v && y, "gemv_rows: null pointer");
+    gemv_rows_kernel<<<(unsigned)pb::ceil_div(rows, 8), 256, 0, stream>>>(m, ld, rows, cols, upper, v, y);
+    return pb::check_launch("gemv_rows");
+}
+
+int pinot_b200_gp_nll_grad(const float* linv_t, int64_t ld, int64_t n, const float* diag_l,
+                           const float* alpha, const float* upstream, int exact_logdet, float* dk,
+                           int64_t lddk, cudaStream_t stream) {
+    // dNLL/dK = 0.5 L^{-T} diag(L) L^{-1} - 0.5 alpha alpha^T      (trace(L) objective)
+    //         = 0.5 L^{-T} L^{-1}         - 0.5 alpha alpha^T      (exact log-det objective)
+    PB_REQUIRE(n >= 0 && n < (1ll << 31) && ld >= n && lddk >= n, "gp_nll_grad: invalid sizes");
+    if (n == 0) return pb::PB_OK;
+    PB_REQUIRE(linv_t && alpha && dk && (exact_logdet || diag_l), "gp_nll_grad: null pointer");
+    pb::GemmParams g;
+    g.M = (int)n; g.N = (int)n; g.K = (int)n;
+    g.A = linv_t; g.lda = ld; g.transA = false;
+    g.B = linv_t; g.ldb = ld; g.transB = true;
+    g.C = dk; g.ldc = lddk;
+    g.alpha = 0.5f; g.beta = 0.f; g.alpha_dev = upstream;
+    g.kscale = exact_logdet ? nullptr : diag_l;
+    g.r1u = alpha; g.r1v = alpha; g.r1coef = -0.5f;
+    g.lower = 1; g.mirror = 1; g.ktri = 1;
+    return pb::gemm(g, stream);
+}
+
+int pinot_b200_gp_predict_mean_var(const float* vt, int64_t ld, int64_t n_te, int64_t n,
+                                   const float* z, const float* variance, float eps, float* mean,
+                                   float* var, cudaStream_t stream) {
+    PB_REQUIRE(n_te >= 0 && n >= 0 && ld >= n, "gp_predict_mean_var: invalid sizes");
+    if (n_te == 0) return pb::PB_OK;
+    PB_REQUIRE(vt && z && mean && (!var || variance), "gp_predict_mean_var: null pointer");
+    gp_predict_kernel<<<(unsigned)pb::ceil_div(n_te, 8), 256, 0, stream>>>(vt, ld, n_te, n, z, variance, eps, mean, var);
+    return pb::check_launch("gp_predict_mean_var");
+}
+
+}  // extern "C"

@@ -1,0 +1,24 @@
+// Error reporting shared by all entry points of the C-ABI library.
+#include "common.cuh"
+#include "../../include/pinot_b200.h"
+
+namespace pb {
+
+static thread_local char g_last_error[512] = {0};
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_last_error, sizeof(g_last_error), fmt, ap);
+    va_end(ap);
+}
+
+}  // namespace pb
+
+extern "C" {
+
+const char* pinot_b200_last_error(void) { return pb::g_last_error; }
+
+int pinot_b200_abi_version(void) { return 1; }
+
+}  // extern "C"

@@ -1,0 +1,33 @@
+// Internal fp32 GEMM used by the node-update layers (kernel 2) and by the trailing updates of the
+// blocked Cholesky sweep (kernel 4).  Row-major everywhere.
+#pragma once
+#include "common.cuh"
+
+namespace pb {
+
+struct GemmParams {
+    int M = 0, N = 0, K = 0;
+    bool transA = false;  // false: A is (M,K) row-major; true: A is stored (K,M)
+    bool transB = false;  // false: B is (K,N) row-major; true: B is stored (N,K)
+    const float* A = nullptr; int64_t lda = 0;
+    const float* B = nullptr; int64_t ldb = 0;
+    float* C = nullptr;       int64_t ldc = 0;
+    float alpha = 1.f, beta = 0.f;
+    const float* alpha_dev = nullptr;  // optional device scalar multiplied into alpha and r1coef
+    const float* bias = nullptr;       // optional [N], added before the activation
+    int act = 0;                       // 0 none, 1 tanh
+    const float* kscale = nullptr;     // optional [K]: op(A)[m,k] *= kscale[k]
+    const float* r1u = nullptr;        // optional rank-1 epilogue: C += r1coef * r1u[m] * r1v[n]
+    const float* r1v = nullptr;
+    float r1coef = 0.f;
+    int lower = 0;   // 1: square-origin C, only elements with n <= m are computed/written
+    int mirror = 0;  // with lower: element (m,n) is also written to (n,m)
+    int ktri = 0;    // 1: op(A)[m,k] == 0 for k < m (and op(B)[k,n] == 0 for k < n): skip k < tile row origin
+    int splitk = 1;  // >1: K is split over grid.z and partial sums are atomically added into C
+                     //     (beta must be 0 or 1; for 0 the caller's C is zeroed by gemm())
+};
+
+// Launches the GEMM on `stream`.  Returns PB_OK or an error code (message via set_error).
+int gemm(const GemmParams& p, cudaStream_t stream);
+
+}  // namespace pb

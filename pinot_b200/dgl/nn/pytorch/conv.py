@@ -1,0 +1,116 @@
+"""Graph convolution layers with DGL's parameter names and arithmetic, on pinot_b200 kernels.
+
+DGL itself is not part of the reference tree (unpinned dependency); the layer
+math follows DGL's documented definitions:
+
+GraphConv(norm="both"):  h_i = in_deg_i^-1/2 * sum_{j->i} out_deg_j^-1/2 x_j, degrees clamped to >= 1,
+    weight (in, out) applied BEFORE aggregation when in > out, AFTER otherwise, then + bias.
+SAGEConv("mean"):        fc_self(x_i) + fc_neigh(mean_{j->i} x_j), the mean of no neighbours being 0.
+"""
+import torch
+
+from .... import ops
+
+__all__ = ["GraphConv", "SAGEConv"]
+
+
+def _csr(graph):
+    if not hasattr(graph, "csr"):
+        raise TypeError("expected a pinot_b200 BatchedGraph, got %r" % type(graph))
+    return graph.csr()
+
+
+class GraphConv(torch.nn.Module):
+    def __init__(self, in_feats, out_feats, norm="both", weight=True, bias=True, activation=None,
+                 allow_zero_in_degree=True):
+        super().__init__()
+        if norm not in ("none", "both", "right"):
+            raise ValueError('Invalid norm value. Must be either "none", "both" or "right".')
+        self._in_feats, self._out_feats, self._norm = in_feats, out_feats, norm
+        self._allow_zero_in_degree = allow_zero_in_degree
+        if weight:
+            self.weight = torch.nn.Parameter(torch.empty(in_feats, out_feats))
+        else:
+            self.register_parameter("weight", None)
+        if bias:
+            self.bias = torch.nn.Parameter(torch.empty(out_feats))
+        else:
+            self.register_parameter("bias", None)
+        self._activation = activation
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        if self.weight is not None:
+            torch.nn.init.xavier_uniform_(self.weight)
+        if self.bias is not None:
+            torch.nn.init.zeros_(self.bias)
+
+    def forward(self, graph, feat, weight=None, _act=None):
+        csr = _csr(graph)
+        if not self._allow_zero_in_degree and csr.has_zero_in_degree:
+            from ... import DGLError
+            raise DGLError("There are 0-in-degree nodes in the graph; set allow_zero_in_degree=True to "
+                           "let their output be the bias only.")
+        w = self.weight if weight is None else weight
+        norm = {"both": "both", "none": "none", "right": "mean"}[self._norm]
+        fuse = _act if self._activation is None else None
+        if w is not None and self._in_feats > self._out_feats:
+            # project first (cheaper), aggregate, then bias (+ activation) as an elementwise tail
+            h = ops.node_update(feat, w, None, w_is_out_in=False)
+            rst = ops.aggregate(h, csr, norm)
+            if self.bias is not None:
+                rst = rst + self.bias
+            if fuse == "tanh":
+                rst = torch.tanh(rst)
+        else:
+            rst = ops.aggregate(feat, csr, norm)
+            if w is not None:
+                rst = ops.node_update(rst, w, self.bias, w_is_out_in=False, act=fuse)
+            else:
+                if self.bias is not None:
+                    rst = rst + self.bias
+                if fuse == "tanh":
+                    rst = torch.tanh(rst)
+        if self._activation is not None:
+            rst = self._activation(rst)
+        return rst
+
+    def extra_repr(self):
+        return "in={_in_feats}, out={_out_feats}, normalization={_norm}".format(**self.__dict__)
+
+
+class SAGEConv(torch.nn.Module):
+    def __init__(self, in_feats, out_feats, aggregator_type="mean", feat_drop=0.0, bias=True, norm=None,
+                 activation=None):
+        super().__init__()
+        if aggregator_type != "mean":
+            raise NotImplementedError(
+                "pinot_b200 SAGEConv implements the 'mean' aggregator (pinot's default, "
+                "pinot/representation/dgl_legacy.py:18-22); got %r" % (aggregator_type,))
+        self._in_feats, self._out_feats = in_feats, out_feats
+        self._aggre_type = aggregator_type
+        self.norm = norm
+        self.feat_drop = torch.nn.Dropout(feat_drop)
+        self.activation = activation
+        self.fc_self = torch.nn.Linear(in_feats, out_feats, bias=bias)
+        self.fc_neigh = torch.nn.Linear(in_feats, out_feats, bias=bias)
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        gain = torch.nn.init.calculate_gain("relu")
+        torch.nn.init.xavier_uniform_(self.fc_self.weight, gain=gain)
+        torch.nn.init.xavier_uniform_(self.fc_neigh.weight, gain=gain)
+
+    def forward(self, graph, feat, _act=None):
+        csr = _csr(graph)
+        feat = self.feat_drop(feat)
+        h_neigh = ops.aggregate(feat, csr, "mean")
+        fuse = _act if (self.activation is None and self.norm is None) else None
+        rst = ops.node_update(feat, self.fc_self.weight, self.fc_self.bias, w_is_out_in=True)
+        rst = ops.node_update(h_neigh, self.fc_neigh.weight, self.fc_neigh.bias, y_prev=rst, w_is_out_in=True,
+                              act=fuse)
+        if self.activation is not None:
+            rst = self.activation(rst)
+        if self.norm is not None:
+            rst = self.norm(rst)
+        return rst

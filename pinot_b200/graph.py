@@ -1,0 +1,267 @@
+"""Batched molecular graph: the stand-in for ``dgl.DGLGraph`` on the hot path.
+
+Follows the layout produced by ``pinot.graph.from_rdkit_mol`` (pinot/graph.py:192-244: node
+features ``ndata["h"]`` (n, 117), edges = all bonds begin->end followed by all bonds end->begin) and
+the batching of ``dgl.batch`` as used by ``pinot.data.utils.batch`` (pinot/data/utils.py:235-282):
+node ids are offset by the cumulative node count, per-graph edge blocks are concatenated in order,
+and per-graph node / edge counts are retained.  Index tensors are int64 like DGL's; the int32 CSR
+views consumed by the kernels are derived once per graph and cached.
+"""
+import contextlib
+
+import torch
+
+
+class GraphCSR:
+    """Device-resident kernel view of a batched graph (built lazily, cached on the graph)."""
+
+    def __init__(self, src, dst, num_nodes, batch_num_nodes):
+        dev = src.device
+        n = int(num_nodes)
+        if src.numel() and (n >= 2 ** 31 or src.numel() >= 2 ** 31):
+            raise ValueError("pinot_b200: graphs are limited to 2^31 nodes / edges (int32 CSR)")
+        src = src.long()
+        dst = dst.long()
+        in_deg = torch.bincount(dst, minlength=n)
+        out_deg = torch.bincount(src, minlength=n)
+        # CSR by destination (forward gather) and by source (transposed graph, backward gather);
+        # stable sorts keep DGL's edge order inside every row.
+        order = torch.sort(dst, stable=True).indices
+        self.indices = src[order].to(torch.int32).contiguous()
+        self.indptr = torch.zeros(n + 1, dtype=torch.int32, device=dev)
+        self.indptr[1:] = torch.cumsum(in_deg, 0).to(torch.int32)
+        order_t = torch.sort(src, stable=True).indices
+        self.indices_t = dst[order_t].to(torch.int32).contiguous()
+        self.indptr_t = torch.zeros(n + 1, dtype=torch.int32, device=dev)
+        self.indptr_t[1:] = torch.cumsum(out_deg, 0).to(torch.int32)
+        # DGL GraphConv(norm="both"): degrees clamped to >= 1, then ^-1/2
+        self.in_norm = in_deg.float().clamp(min=1).pow(-0.5).contiguous()
+        self.out_norm = out_deg.float().clamp(min=1).pow(-0.5).contiguous()
+        # SAGEConv("mean"): mean over in-neighbours, 0 for isolated nodes
+        self.inv_in_deg = (1.0 / in_deg.float().clamp(min=1)).contiguous()
+        bnn = torch.as_tensor(batch_num_nodes, dtype=torch.long, device=dev)
+        self.batch_size = int(bnn.numel())
+        self.seg_offsets = torch.zeros(self.batch_size + 1, dtype=torch.int32, device=dev)
+        self.seg_offsets[1:] = torch.cumsum(bnn, 0).to(torch.int32)
+        self.node_seg = torch.repeat_interleave(
+            torch.arange(self.batch_size, device=dev, dtype=torch.int32), bnn
+        ).contiguous()
+        self.num_nodes = n
+        self.has_zero_in_degree = bool((in_deg == 0).any().item()) if n else False
+
+    def scales(self, norm):
+        if norm == "both":
+            return self.out_norm, self.in_norm
+        if norm == "mean":
+            return None, self.inv_in_deg
+        if norm == "none":
+            return None, None
+        raise ValueError("unknown norm %r" % (norm,))
+
+
+class _Frame(dict):
+    """``g.ndata`` / ``g.edata``: a dict of per-node (per-edge) tensors with a length check."""
+
+    def __init__(self, owner, count_fn):
+        super().__init__()
+        self._count_fn = count_fn
+
+    def __setitem__(self, key, value):
+        n = self._count_fn()
+        if torch.is_tensor(value) and value.shape[0] != n:
+            raise ValueError("expected %d rows for feature %r, got %d" % (n, key, value.shape[0]))
+        super().__setitem__(key, value)
+
+
+class BatchedGraph:
+    """A batch of graphs with DGL-compatible surface (``ndata``, ``local_scope``, ``to``,
+    ``batch_size``, ``number_of_nodes`` ...) used by pinot's representation, data and active-learning
+    code (pinot/representation/sequential.py:78-103, pinot/data/utils.py:260-276,
+    pinot/active/experiment.py:99-104)."""
+
+    def __init__(self, src=None, dst=None, num_nodes=0, batch_num_nodes=None, batch_num_edges=None):
+        self._src = torch.zeros(0, dtype=torch.long) if src is None else torch.as_tensor(src, dtype=torch.long)
+        self._dst = torch.zeros(0, dtype=torch.long) if dst is None else torch.as_tensor(dst, dtype=torch.long).to(self._src.device)
+        if self._src.shape != self._dst.shape:
+            raise ValueError("src and dst must have the same length")
+        self._num_nodes = int(num_nodes)
+        self._bnn = [self._num_nodes] if batch_num_nodes is None else [int(v) for v in batch_num_nodes]
+        self._bne = [int(self._src.numel())] if batch_num_edges is None else [int(v) for v in batch_num_edges]
+        if sum(self._bnn) != self._num_nodes or sum(self._bne) != self._src.numel():
+            raise ValueError("per-graph counts do not add up to the totals")
+        if self._src.numel():
+            hi = int(max(self._src.max().item(), self._dst.max().item()))
+            lo = int(min(self._src.min().item(), self._dst.min().item()))
+            if lo < 0 or hi >= self._num_nodes:
+                raise ValueError("edge endpoint out of range [0, %d)" % self._num_nodes)
+        self.ndata = _Frame(self, lambda: self._num_nodes)
+        self.edata = _Frame(self, lambda: int(self._src.numel()))
+        self._csr = None
+
+    # -- construction in the style of pinot/graph.py:208-239 -----------------------------------
+    def add_nodes(self, n):
+        if self._src.numel() or len(self._bnn) != 1:
+            raise RuntimeError("add_nodes is only supported while building a single empty graph")
+        self._num_nodes += int(n)
+        self._bnn = [self._num_nodes]
+        self._csr = None
+
+    def add_edges(self, u, v, data=None):
+        if len(self._bnn) != 1:
+            raise RuntimeError("add_edges is only supported on a single (unbatched) graph")
+        u = torch.as_tensor(u, dtype=torch.long, device=self._src.device).reshape(-1)
+        v = torch.as_tensor(v, dtype=torch.long, device=self._src.device).reshape(-1)
+        if u.numel() != v.numel():
+            raise ValueError("add_edges: endpoint lists differ in length")
+        if u.numel() and (int(min(u.min(), v.min())) < 0 or int(max(u.max(), v.max())) >= self._num_nodes):
+            raise ValueError("add_edges: endpoint out of range")
+        self._src = torch.cat([self._src, u])
+        self._dst = torch.cat([self._dst, v])
+        self._bne = [int(self._src.numel())]
+        n_new = int(u.numel())
+        n_old = int(self._src.numel()) - n_new
+        for k in list(self.edata.keys()):
+            old = self.edata[k]
+            new = None if data is None else data.get(k)
+            if new is None:
+                new = torch.zeros((n_new,) + tuple(old.shape[1:]), dtype=old.dtype, device=old.device)
+            dict.__setitem__(self.edata, k, torch.cat([old, torch.as_tensor(new, dtype=old.dtype)], dim=0))
+        if data is not None:
+            for k, new in data.items():
+                if k not in self.edata:
+                    new = torch.as_tensor(new)
+                    pad = torch.zeros((n_old,) + tuple(new.shape[1:]), dtype=new.dtype)
+                    dict.__setitem__(self.edata, k, torch.cat([pad, new], dim=0))
+        self._csr = None
+
+    # -- DGL surface ----------------------------------------------------------------------------
+    @property
+    def batch_size(self):
+        return len(self._bnn)
+
+    def number_of_nodes(self):
+        return self._num_nodes
+
+    num_nodes = number_of_nodes
+
+    def number_of_edges(self):
+        return int(self._src.numel())
+
+    num_edges = number_of_edges
+
+    def batch_num_nodes(self):
+        return torch.tensor(self._bnn, dtype=torch.long)
+
+    def batch_num_edges(self):
+        return torch.tensor(self._bne, dtype=torch.long)
+
+    def edges(self):
+        return self._src, self._dst
+
+    def all_edges(self):
+        return self.edges()
+
+    def in_degrees(self):
+        return torch.bincount(self._dst, minlength=self._num_nodes)
+
+    def out_degrees(self):
+        return torch.bincount(self._src, minlength=self._num_nodes)
+
+    @property
+    def device(self):
+        return self._src.device
+
+    def to(self, device, **kwargs):
+        g = BatchedGraph.__new__(BatchedGraph)
+        g._src = self._src.to(device)
+        g._dst = self._dst.to(device)
+        g._num_nodes = self._num_nodes
+        g._bnn = list(self._bnn)
+        g._bne = list(self._bne)
+        g.ndata = _Frame(g, lambda: g._num_nodes)
+        g.edata = _Frame(g, lambda: int(g._src.numel()))
+        for k, v in self.ndata.items():
+            dict.__setitem__(g.ndata, k, v.to(device) if torch.is_tensor(v) else v)
+        for k, v in self.edata.items():
+            dict.__setitem__(g.edata, k, v.to(device) if torch.is_tensor(v) else v)
+        g._csr = self._csr if (self._csr is not None and torch.device(device) == self._src.device) else None
+        return g
+
+    @contextlib.contextmanager
+    def local_scope(self):
+        saved_n = dict(self.ndata)
+        saved_e = dict(self.edata)
+        try:
+            yield self
+        finally:
+            dict.clear(self.ndata)
+            dict.update(self.ndata, saved_n)
+            dict.clear(self.edata)
+            dict.update(self.edata, saved_e)
+
+    def local_var(self):
+        g = self.to(self.device)
+        g._csr = self._csr
+        return g
+
+    def __repr__(self):
+        return "BatchedGraph(batch_size=%d, num_nodes=%d, num_edges=%d, device=%s)" % (
+            self.batch_size, self._num_nodes, self.number_of_edges(), self.device)
+
+    # -- kernel view ----------------------------------------------------------------------------
+    def csr(self):
+        if self._csr is None:
+            self._csr = GraphCSR(self._src, self._dst, self._num_nodes, self._bnn)
+        return self._csr
+
+
+def batch(graphs):
+    """``dgl.batch``: concatenate graphs; node ids of graph k are offset by the nodes before it."""
+    graphs = list(graphs)
+    if not graphs:
+        raise ValueError("batch() needs at least one graph")
+    srcs, dsts, bnn, bne = [], [], [], []
+    offset = 0
+    for g in graphs:
+        srcs.append(g._src + offset)
+        dsts.append(g._dst + offset)
+        bnn.extend(g._bnn)
+        bne.extend(g._bne)
+        offset += g._num_nodes
+    out = BatchedGraph(torch.cat(srcs), torch.cat(dsts), offset, bnn, bne)
+    for frame_name in ("ndata", "edata"):
+        keys = set(getattr(graphs[0], frame_name).keys())
+        for g in graphs[1:]:
+            keys &= set(getattr(g, frame_name).keys())
+        for k in sorted(keys):
+            dict.__setitem__(getattr(out, frame_name), k,
+                             torch.cat([getattr(g, frame_name)[k] for g in graphs], dim=0))
+    return out
+
+
+def unbatch(g):
+    """``dgl.unbatch``: the inverse of :func:`batch`."""
+    out = []
+    n0 = e0 = 0
+    for n, e in zip(g._bnn, g._bne):
+        sub = BatchedGraph(g._src[e0:e0 + e] - n0, g._dst[e0:e0 + e] - n0, n)
+        for k, v in g.ndata.items():
+            dict.__setitem__(sub.ndata, k, v[n0:n0 + n])
+        for k, v in g.edata.items():
+            dict.__setitem__(sub.edata, k, v[e0:e0 + e])
+        out.append(sub)
+        n0 += n
+        e0 += e
+    return out
+
+
+def sum_nodes(g, feat):
+    """``dgl.sum_nodes(g, feat)``: per-graph sum of a node feature -> (batch_size, F)."""
+    from . import ops
+    return ops.segment_readout(g.ndata[feat], g.csr(), mean=False)
+
+
+def mean_nodes(g, feat):
+    """``dgl.mean_nodes(g, feat)``."""
+    from . import ops
+    return ops.segment_readout(g.ndata[feat], g.csr(), mean=True)
