@@ -1,0 +1,356 @@
+"""Benchmark of the GCN + exact-GP train step (BASELINE.json metric: molecules/s).
+
+    python bench.py --gpus N --steps K --warmup W            # the B200 path (one process per GPU)
+    python bench.py --impl reference --steps K --warmup W    # the reference's CPU arithmetic (oracle port)
+
+Workload (BASELINE.json configs[1], SURVEY.md section 8d "C2"): 4 200 synthetic molecules per GPU
+(~25 atoms / ~54 directed edges each), GraphConv 3x128 + tanh, sum readout, exact GP with pinot's
+RBF kernel, full-batch objective; one step = zero_grad -> Net.loss -> backward -> (gradient
+all-reduce when N > 1) -> Adam.step, as in pinot/app/experiment.py:78-89.  Weak scaling: every rank
+trains on its own 4 200-molecule batch and the ranks exchange ONE flat gradient all-reduce per step.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "molecules/sec (GCN+GP train step)"
+UNIT = "molecules/s"
+CONFIG = [128, "tanh", 128, "tanh", 128, "tanh"]
+N_MOL = 4200
+HIDDEN = 128
+KERNEL_SCALE = -3.0  # "trained-like" length-scale: at init K is numerically the identity
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--molecules", type=int, default=N_MOL)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def workload_config(n_mol, world):
+    return {
+        "workload": "C2: %d synthetic molecules per GPU (25 atoms / 54 directed edges), GraphConv 3x128 + "
+                    "exact GP (RBF), full-batch marginal likelihood, Adam" % n_mol,
+        "molecules_per_gpu": n_mol, "global_molecules": n_mol * world, "hidden": HIDDEN,
+        "kernel_scale_init": KERNEL_SCALE, "parallelism": "dp%d (gradient all-reduce)" % world,
+        "l2": "flushed between timed steps (256 MiB write)",
+    }
+
+
+# --------------------------------------------------------------------------------------------------
+# CPU arm: the oracle's restatement of the reference arithmetic (the reference itself needs DGL and
+# is not present on the GPU box)
+# --------------------------------------------------------------------------------------------------
+def cpu_arm(n_mol, steps, warmup, seed=2666, budget_s=170.0):
+    """Times zero_grad -> loss -> backward -> Adam.step of the reference arithmetic on the host
+    cores.  Returns (molecules/s, ms_per_step, cores, sample description)."""
+    from oracle import net_ref
+    from pinot_b200 import synthetic
+    import psutil
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+
+    def build(n):
+        g, y = synthetic.make_batch(n, seed=seed)
+        s, d = g.edges()
+        rg = net_ref.graph_from_arrays(s, d, g.number_of_nodes(), g.batch_num_nodes().tolist(),
+                                       g.batch_num_edges().tolist(), g.ndata["h"])
+        torch.manual_seed(0)
+        params = init_state(HIDDEN)
+        p = {k: v.clone().requires_grad_(True) for k, v in params.items()}
+        opt = torch.optim.Adam(list(p.values()), 1e-3)
+        return rg, y, p, opt
+
+    def step(rg, y, p, opt):
+        opt.zero_grad()
+        loss, _ = net_ref.exact_net_loss(rg, y, p, CONFIG)
+        loss.sum().backward()
+        opt.step()
+        return float(loss.sum())
+
+    # the reference materialises an (N, N, 128) fp32 tensor several times over (forward, norm,
+    # backward): ~9 GB per copy at N = 4200
+    avail = psutil.virtual_memory().available / 2 ** 30
+    n = n_mol if avail > 110 else min(n_mol, 1128)
+    rg, y, p, opt = build(n)
+    t0 = time.perf_counter()
+    step(rg, y, p, opt)
+    first = time.perf_counter() - t0
+    done_warm = 1
+    if n > 1128 and first * (steps + max(warmup - 1, 0)) > budget_s:
+        n = 1128
+        rg, y, p, opt = build(n)
+        done_warm = 0
+    for _ in range(max(warmup - done_warm, 0)):
+        step(rg, y, p, opt)
+    times = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        step(rg, y, p, opt)
+        times.append(time.perf_counter() - t0)
+    ms = 1e3 * sum(times) / len(times)
+    sample = ("%d of the %d molecules per step (same generator and seed), %d timed steps after %d warm-up, "
+              "torch CPU fp32 with %d threads; oracle port of the reference arithmetic (N x N x D broadcast "
+              "distance, torch Cholesky, autograd)" % (n, n_mol, steps, warmup, cores))
+    return n / (ms * 1e-3), ms, cores, sample
+
+
+def init_state(hidden):
+    """Reference-style initialisation as a plain state_dict (shared by both arms)."""
+    import pinot_b200 as pb
+    net = pb.Net(pb.representation.Sequential(pb.representation.dgl_legacy.gn(), CONFIG, input_units=hidden),
+                 output_regressor_class=pb.regressors.ExactGaussianProcessRegressor)
+    with torch.no_grad():
+        net.output_regressor.kernel.scale.fill_(KERNEL_SCALE)
+    return {k: v.detach().clone() for k, v in net.state_dict().items()}
+
+
+def reference_main(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    value, ms, cores, sample = cpu_arm(args.molecules, args.steps, args.warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args.molecules, 1),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# --------------------------------------------------------------------------------------------------
+# B200 arm
+# --------------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu_index = gpu_index
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "--query-gpu=" + self.FIELDS, "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+            out, _ = self.proc.communicate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in out.splitlines():
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 8 or parts[0] != str(self.gpu_index):
+                continue
+            try:
+                sm.append(float(parts[1]))
+                mx = float(parts[2])
+            except ValueError:
+                continue
+            for nm, val in zip(names, parts[4:8]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return p.get("hbm_gbs", 6650.0), p.get("bf16_tflops_sustained", 1400.0), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, 1400.0, "fallback (B200_PROFILING.md)"
+
+
+def b200_main(args):
+    import pinot_b200 as pb
+    from pinot_b200 import _lib, distributed as pbd, synthetic
+    from pinot_b200.graph import BatchedGraph
+
+    rank, world, local_rank = pbd.init_from_env()
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    _lib.load()
+    n_mol = args.molecules
+
+    # ---- workload: this rank's batch, resident in HBM ----
+    g_host, y_host = synthetic.make_batch(n_mol, seed=2666 + rank)
+    g = g_host.to(dev)
+    y = y_host.to(dev)
+    g.csr()
+    torch.manual_seed(0)
+    net = pb.Net(pb.representation.Sequential(pb.representation.dgl_legacy.gn(), CONFIG, input_units=HIDDEN),
+                 output_regressor_class=pb.regressors.ExactGaussianProcessRegressor)
+    net.load_state_dict(init_state(HIDDEN))
+    net = net.to(dev)
+    pbd.broadcast_parameters(net)
+    opt = torch.optim.Adam(net.parameters(), 1e-3)
+    bucket = pbd.GradientBucket(net.parameters())
+    flush_buf = torch.empty(64 * 2 ** 20, dtype=torch.float32, device=dev)  # 256 MiB > 126 MB L2
+
+    def step(graph, target):
+        opt.zero_grad(set_to_none=True)
+        loss = net.loss(graph, target).sum()
+        loss.backward()
+        bucket.allreduce(average=False)
+        opt.step()
+        return loss
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step(g, y)
+    barrier()
+
+    probe_names = ["gp_nll_grad", "mp_csr_aggregate_fwd", "mp_csr_aggregate_bwd", "potrf_ext", "gram_fwd", "gram_bwd",
+                   "node_update_fwd", "node_update_bwd", "segment_readout_fwd"]
+    _lib.probe = {k: [] for k in probe_names}
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    launches0 = _lib.launch_count()
+    evs = []
+    barrier()
+    for _ in range(args.steps):
+        flush_buf.zero_()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        loss = step(g, y)
+        e.record()
+        evs.append((s, e))
+    barrier()
+    launches = _lib.launch_count() - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    probes, _lib.probe = _lib.probe, None
+    step_ms = [s.elapsed_time(e) for s, e in evs]
+    total_ms = pbd.max_over_ranks(sum(step_ms), dev)
+    ms_per_step = total_ms / args.steps
+    value = n_mol * world / (ms_per_step * 1e-3)
+    final_loss = float(loss)
+
+    # ---- per-kernel timings from the probes (CUDA events on the launching stream, timed region) ----
+    def probe_ms(name):
+        ev = probes.get(name, [])
+        return (sum(s.elapsed_time(e) for s, e in ev) / len(ev), len(ev)) if ev else (None, 0)
+
+    hbm_peak, tf_peak, peak_src = measured_peaks()
+    nn_, ne_ = g.number_of_nodes(), g.number_of_edges()
+    shares = {}
+    for k in probe_names:
+        ms, cnt = probe_ms(k)
+        if ms is not None:
+            shares[k] = {"ms_per_call": ms, "calls_per_step": cnt / args.steps,
+                         "share_of_step": ms * cnt / args.steps / ms_per_step}
+    grad_ms, _ = probe_ms("gp_nll_grad")
+    n = n_mol
+    grad_flop = n ** 3 / 3.0  # L^-T diag(L) L^-1, both factors triangular, symmetric result
+    roofline = {
+        "kernel": "sgemm_kernel<NT> in pinot_b200_gp_nll_grad (closed-form marginal-likelihood gradient, N=%d)" % n,
+        "bound": "tensor", "achieved": grad_flop / (grad_ms * 1e-3) / 1e12 if grad_ms else None,
+        "peak": tf_peak, "unit": "TFLOP/s", "peak_source": peak_src + ", bf16 sustained",
+        "traffic": None,
+        "note": "fp32 FFMA kernel (fp32 parity path); fraction is against the bf16 tensor-core peak",
+    }
+    if roofline["achieved"] is not None:
+        roofline["frac"] = roofline["achieved"] / tf_peak
+    agg_ms, _ = probe_ms("mp_csr_aggregate_fwd")
+    agg_bytes = 4.0 * HIDDEN * nn_ * 2 + 4.0 * ne_ + 4.0 * (nn_ + 1) + 8.0 * nn_
+    extra = []
+    if agg_ms:
+        a = agg_bytes / (agg_ms * 1e-3) / 1e9
+        extra.append({"kernel": "mp_aggregate_kernel<4> (fwd)", "bound": "hbm", "achieved": a, "peak": hbm_peak,
+                      "unit": "GB/s", "frac": a / hbm_peak, "bytes_per_launch": agg_bytes,
+                      "note": "C2 activations (54 MB) are L2-resident inside the step; HBM-sized run: "
+                              "benchmarks/kernel_bench.py"})
+
+    # ---- end-to-end: host buffers in, loss out, every step (public API) ----
+    e2e = None
+    if not args.no_e2e:
+        src_h, dst_h = (t.pin_memory() for t in g_host.edges())
+        feat_h = g_host.ndata["h"].pin_memory()
+        y_h = y_host.pin_memory()
+        bnn, bne = g_host.batch_num_nodes().tolist(), g_host.batch_num_edges().tolist()
+        h2d = sum(t.numel() * t.element_size() for t in (src_h, dst_h, feat_h, y_h))
+
+        def e2e_step():
+            gs = BatchedGraph(src_h.to(dev, non_blocking=True), dst_h.to(dev, non_blocking=True),
+                              g_host.number_of_nodes(), bnn, bne, validate=False)
+            gs.ndata["h"] = feat_h.to(dev, non_blocking=True)
+            yy = y_h.to(dev, non_blocking=True)
+            return float(step(gs, yy).item())   # device -> host read of the loss
+
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_step()
+        barrier()
+        e2e_s = pbd.max_over_ranks(time.perf_counter() - t0, dev)
+        e2e = {"value": n_mol * world * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": 4, "ms_per_step": 1e3 * e2e_s / args.steps,
+               "includes": "H2D of edges/features/targets from pinned memory, CSR build, train step, loss.item()"}
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        v, ms, cores, sample = cpu_arm(n_mol, steps=2, warmup=1, budget_s=40.0)
+        cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                        "ms_per_step": ms}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(n_mol, world),
+            "roofline": roofline, "roofline_other_kernels": extra, "kernel_shares": shares,
+            "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+            "final_loss": final_loss,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        torch.distributed.barrier()
+        torch.distributed.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    a = parse()
+    sys.exit(reference_main(a) if a.impl == "reference" else b200_main(a))

@@ -37,6 +37,8 @@ typedef struct CUstream_st* cudaStream_t;
 PINOT_B200_API const char* pinot_b200_last_error(void);
 /* ABI version of this header (bumped on any signature change). */
 PINOT_B200_API int pinot_b200_abi_version(void);
+/* Number of CUDA kernels this library has launched so far in the calling process. */
+PINOT_B200_API int64_t pinot_b200_launch_count(void);
 
 /* ---------------------------------------------------------------------------------------------
  * Kernel (1): message passing.

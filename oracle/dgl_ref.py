@@ -61,16 +61,10 @@ class DGLGraph:
         return [len(self.src)] if self.batch_edges is None else list(self.batch_edges)
 
     def in_degrees(self):
-        d = torch.zeros(self.n, dtype=torch.long)
-        for j in self.dst:
-            d[j] += 1
-        return d
+        return torch.bincount(torch.tensor(self.dst, dtype=torch.long), minlength=self.n)
 
     def out_degrees(self):
-        d = torch.zeros(self.n, dtype=torch.long)
-        for j in self.src:
-            d[j] += 1
-        return d
+        return torch.bincount(torch.tensor(self.src, dtype=torch.long), minlength=self.n)
 
     def to(self, device, **kw):
         return self

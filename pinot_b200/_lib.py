@@ -21,6 +21,7 @@ _ptr = ctypes.c_void_p
 SIGNATURES = {
     "pinot_b200_last_error": [],
     "pinot_b200_abi_version": [],
+    "pinot_b200_launch_count": [],
     "pinot_b200_mp_csr_aggregate_fwd": [_ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i64, _ptr],
     "pinot_b200_mp_csr_aggregate_bwd": [_ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i64, _ptr],
     "pinot_b200_segment_readout_fwd": [_ptr, _ptr, _ptr, _i64, _i64, _i32, _ptr],
@@ -42,6 +43,7 @@ SIGNATURES = {
 _RESTYPES = {
     "pinot_b200_last_error": ctypes.c_char_p,
     "pinot_b200_potrf_workspace_bytes": ctypes.c_int64,
+    "pinot_b200_launch_count": ctypes.c_int64,
 }
 
 _lib = None
@@ -91,14 +93,31 @@ def ptr(t):
     return t.data_ptr()
 
 
+# optional timing probes: {entry point name: [(start_event, end_event), ...]} -- bench.py uses this to
+# time chosen kernels with CUDA events on the launching stream inside the timed region
+probe = None
+
+
 def call(name, *args):
     """Invoke an int-returning entry point on the current stream; raise on a non-zero code."""
     global call_count
     lib = load()
-    rc = getattr(lib, "pinot_b200_" + name)(*args, stream_ptr())
+    if probe is not None and name in probe:
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        rc = getattr(lib, "pinot_b200_" + name)(*args, stream_ptr())
+        e.record()
+        probe[name].append((s, e))
+    else:
+        rc = getattr(lib, "pinot_b200_" + name)(*args, stream_ptr())
     call_count += 1
     if rc != 0:
         raise PinotB200Error("pinot_b200_%s failed (code %d): %s" % (name, rc, last_error()))
+
+
+def launch_count():
+    """Kernels launched by the library so far in this process."""
+    return int(load().pinot_b200_launch_count())
 
 
 def potrf_workspace_bytes(n):

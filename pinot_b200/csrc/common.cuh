@@ -18,7 +18,11 @@ enum : int {
     PB_ERR_LIMIT = 3,    // size exceeds a documented limit
 };
 
+// Number of kernels this library has launched in the process (bench.py's gpu_launches claim).
+void count_launch();
+
 inline int check_launch(const char* what) {
+    count_launch();
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         set_error("%s: CUDA error %d (%s)", what, (int)e, cudaGetErrorString(e));

@@ -79,7 +79,7 @@ class BatchedGraph:
     code (pinot/representation/sequential.py:78-103, pinot/data/utils.py:260-276,
     pinot/active/experiment.py:99-104)."""
 
-    def __init__(self, src=None, dst=None, num_nodes=0, batch_num_nodes=None, batch_num_edges=None):
+    def __init__(self, src=None, dst=None, num_nodes=0, batch_num_nodes=None, batch_num_edges=None, validate=True):
         self._src = torch.zeros(0, dtype=torch.long) if src is None else torch.as_tensor(src, dtype=torch.long)
         self._dst = torch.zeros(0, dtype=torch.long) if dst is None else torch.as_tensor(dst, dtype=torch.long).to(self._src.device)
         if self._src.shape != self._dst.shape:
@@ -87,9 +87,9 @@ class BatchedGraph:
         self._num_nodes = int(num_nodes)
         self._bnn = [self._num_nodes] if batch_num_nodes is None else [int(v) for v in batch_num_nodes]
         self._bne = [int(self._src.numel())] if batch_num_edges is None else [int(v) for v in batch_num_edges]
-        if sum(self._bnn) != self._num_nodes or sum(self._bne) != self._src.numel():
+        if validate and (sum(self._bnn) != self._num_nodes or sum(self._bne) != self._src.numel()):
             raise ValueError("per-graph counts do not add up to the totals")
-        if self._src.numel():
+        if validate and self._src.numel():
             hi = int(max(self._src.max().item(), self._dst.max().item()))
             lo = int(min(self._src.min().item(), self._dst.min().item()))
             if lo < 0 or hi >= self._num_nodes:

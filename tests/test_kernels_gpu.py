@@ -1,0 +1,345 @@
+"""Per-kernel parity: each C-ABI kernel against the CPU oracle on the same seeded inputs.
+
+Tolerances: index work is bit-exact; fp32 results within 1e-4 relative of the oracle (north_star);
+gradients within 1e-3 (they are compared with fp64 autograd of the oracle)."""
+import pytest
+import torch
+
+import pinot_b200 as pb
+from pinot_b200 import ops, synthetic
+from conftest import rel_err, max_rel_err
+from oracle import dgl_ref, gp_ref
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _ref_graph(g, dtype=torch.float32):
+    s, d = g.edges()
+    return dgl_ref.from_arrays(s.cpu(), d.cpu(), g.number_of_nodes(), g.batch_num_nodes().tolist(),
+                               g.batch_num_edges().tolist())
+
+
+# ---------------------------------------------------------------------------------------------
+# kernel (1)
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("feat", [128, 32, 20, 7, 1])
+@pytest.mark.parametrize("norm", ["both", "mean", "none"])
+def test_aggregate_fwd_bwd(feat, norm):
+    torch.manual_seed(feat)
+    g, _ = synthetic.make_batch(40, seed=11, mean_atoms=10, std_atoms=6)
+    single = pb.BatchedGraph(num_nodes=1)   # zero-in-degree node
+    single.ndata["h"] = torch.zeros(1, 117)
+    g = pb.batch([g, single])
+    rg = _ref_graph(g)
+    n = g.number_of_nodes()
+    x = torch.randn(n, feat)
+    go = torch.randn(n, feat)
+    xr = x.double().requires_grad_(True)
+    want = dgl_ref.graph_conv(rg, xr, None, None, {"both": "both", "mean": "right", "none": "none"}[norm])
+    want.backward(go.double())
+    gd = g.to(DEV)
+    xd = x.to(DEV).requires_grad_(True)
+    got = ops.aggregate(xd, gd.csr(), norm)
+    got.backward(go.to(DEV))
+    assert rel_err(got, want) < 1e-6
+    assert max_rel_err(got, want) < 1e-4
+    assert rel_err(xd.grad, xr.grad) < 1e-6
+
+
+def test_aggregate_empty_graph_and_no_edges():
+    g = pb.batch([pb.BatchedGraph(num_nodes=2), pb.BatchedGraph(num_nodes=1)])
+    gd = g.to(DEV)
+    x = torch.randn(3, 8, device=DEV)
+    assert torch.count_nonzero(ops.aggregate(x, gd.csr(), "both")) == 0
+    out = ops.segment_readout(x, gd.csr())
+    assert torch.allclose(out[0], x[:2].sum(0)) and torch.allclose(out[1], x[2])
+
+
+@pytest.mark.parametrize("feat", [128, 33])
+@pytest.mark.parametrize("mean", [False, True])
+def test_segment_readout_fwd_bwd(feat, mean):
+    g, _ = synthetic.make_batch(50, seed=12, mean_atoms=9, std_atoms=5)
+    rg = _ref_graph(g)
+    n = g.number_of_nodes()
+    x = torch.randn(n, feat)
+    go = torch.randn(50, feat)
+    xr = x.double().requires_grad_(True)
+    rg.ndata["h"] = xr
+    want = dgl_ref.mean_nodes(rg, "h") if mean else dgl_ref.sum_nodes(rg, "h")
+    want.backward(go.double())
+    gd = g.to(DEV)
+    xd = x.to(DEV).requires_grad_(True)
+    gd.ndata["h"] = xd
+    got = (pb.graph.mean_nodes if mean else pb.graph.sum_nodes)(gd, "h")
+    got.backward(go.to(DEV))
+    assert got.shape == (50, feat)
+    assert rel_err(got, want) < 1e-6 and rel_err(xd.grad, xr.grad) < 1e-6
+
+
+# ---------------------------------------------------------------------------------------------
+# kernel (2)
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n,fin,fout", [(1000, 117, 128), (517, 128, 128), (300, 128, 32), (131, 20, 7), (1, 5, 3)])
+@pytest.mark.parametrize("w_is_out_in", [True, False])
+@pytest.mark.parametrize("act", [None, "tanh"])
+def test_node_update_fwd_bwd(n, fin, fout, w_is_out_in, act):
+    torch.manual_seed(n + fin)
+    x = torch.randn(n, fin)
+    w = torch.randn(fout, fin) * 0.1 if w_is_out_in else torch.randn(fin, fout) * 0.1
+    b = torch.randn(fout)
+    go = torch.randn(n, fout)
+    xr, wr, br = (t.double().requires_grad_(True) for t in (x, w, b))
+    want = xr @ (wr.t() if w_is_out_in else wr) + br
+    if act:
+        want = torch.tanh(want)
+    want.backward(go.double())
+    xd, wd, bd = (t.to(DEV).requires_grad_(True) for t in (x, w, b))
+    got = ops.node_update(xd, wd, bd, w_is_out_in=w_is_out_in, act=act)
+    got.backward(go.to(DEV))
+    assert rel_err(got, want) < 2e-6
+    assert rel_err(xd.grad, xr.grad) < 1e-5
+    assert rel_err(wd.grad, wr.grad) < 1e-5
+    assert rel_err(bd.grad, br.grad) < 1e-5
+
+
+def test_node_update_large_rows_uses_split_k_weight_gradient():
+    torch.manual_seed(0)
+    n, f = 30000, 128
+    x = torch.randn(n, f, device=DEV)
+    w = (0.05 * torch.randn(f, f, device=DEV)).requires_grad_(True)
+    b = torch.zeros(f, device=DEV, requires_grad=True)
+    go = torch.randn(n, f, device=DEV)
+    y = ops.node_update(x, w, b, w_is_out_in=False, act="tanh")
+    y.backward(go)
+    yr = torch.tanh(x.double() @ w.detach().double())
+    dz = go.double() * (1 - yr * yr)
+    assert rel_err(y, yr) < 2e-6
+    assert rel_err(w.grad, x.double().t() @ dz) < 1e-5
+    assert rel_err(b.grad, dz.sum(0)) < 1e-5
+
+
+def test_node_update_accumulate_for_sage():
+    torch.manual_seed(1)
+    x, hn = torch.randn(200, 64, device=DEV), torch.randn(200, 64, device=DEV)
+    ws, wn = torch.randn(48, 64, device=DEV) * 0.1, torch.randn(48, 64, device=DEV) * 0.1
+    bs, bn = torch.randn(48, device=DEV), torch.randn(48, device=DEV)
+    y = ops.node_update(x, ws, bs, w_is_out_in=True)
+    y = ops.node_update(hn, wn, bn, y_prev=y, w_is_out_in=True, act="tanh")
+    want = torch.tanh(x.double() @ ws.double().t() + bs.double() + hn.double() @ wn.double().t() + bn.double())
+    assert rel_err(y, want) < 2e-6
+
+
+@pytest.mark.parametrize("ta", [False, True])
+@pytest.mark.parametrize("tb", [False, True])
+@pytest.mark.parametrize("m,n,k", [(257, 130, 77), (64, 64, 4096), (5, 3, 2), (128, 128, 128), (300, 1, 50)])
+def test_sgemm_all_layouts(ta, tb, m, n, k):
+    torch.manual_seed(m * n + k)
+    a = torch.randn((k, m) if ta else (m, k))
+    b = torch.randn((n, k) if tb else (k, n))
+    want = (a.double().t() if ta else a.double()) @ (b.double().t() if tb else b.double())
+    ad, bd = a.to(DEV).requires_grad_(True), b.to(DEV).requires_grad_(True)
+    got = ops.matmul(ad, bd, ta, tb)
+    assert rel_err(got, want) < 2e-6
+    go = torch.randn(m, n)
+    got.backward(go.to(DEV))
+    ar, br = a.double().requires_grad_(True), b.double().requires_grad_(True)
+    ((ar.t() if ta else ar) @ (br.t() if tb else br)).backward(go.double())
+    assert rel_err(ad.grad, ar.grad) < 1e-5 and rel_err(bd.grad, br.grad) < 1e-5
+
+
+# ---------------------------------------------------------------------------------------------
+# kernel (3)
+# ---------------------------------------------------------------------------------------------
+def _kernel_params(kind, d, scale, variance):
+    sc = torch.full((d,), scale) if kind == "rbf" else torch.tensor(scale)
+    return sc, torch.tensor(variance)
+
+
+@pytest.mark.parametrize("kind", ["rbf", "matern52"])
+@pytest.mark.parametrize("n,n2,d", [(300, 300, 128), (131, 67, 32), (64, 200, 7), (1, 5, 3), (70, 70, 200)])
+def test_gram_forward(kind, n, n2, d):
+    torch.manual_seed(n + d)
+    x, y = torch.randn(n, d) * 0.6, torch.randn(n2, d) * 0.6
+    y[: min(n, n2) // 2] = x[: min(n, n2) // 2]      # duplicate rows: exact zero distances off the diagonal too
+    sc, var = _kernel_params(kind, d, -0.7, 0.4)
+    want = gp_ref.KERNELS[kind](x, y, sc, var)
+    got = ops.gram(kind, x.to(DEV), y.to(DEV), sc.to(DEV), var.to(DEV))
+    assert got.shape == (n, n2)
+    assert max_rel_err(got, want) < 1e-4, "K must match the difference-form reference to 1e-4 relative"
+    # fused _perturb on a rectangular matrix: +eps on the main diagonal only
+    got_p = ops.gram(kind, x.to(DEV), y.to(DEV), sc.to(DEV), var.to(DEV), diag_add=1e-5)
+    assert max_rel_err(got_p, gp_ref.perturb(want)) < 1e-4
+    # K(x, x): exact amplitude on the diagonal
+    kxx = ops.gram(kind, x.to(DEV), None, sc.to(DEV), var.to(DEV))
+    assert torch.allclose(torch.diagonal(kxx).cpu(), torch.exp(var).expand(n), rtol=1e-6)
+    assert torch.equal(kxx, kxx.t())
+
+
+@pytest.mark.parametrize("kind", ["rbf", "matern52"])
+@pytest.mark.parametrize("n,n2,d", [(150, 150, 128), (97, 41, 32), (40, 90, 7), (33, 33, 200)])
+def test_gram_backward_two_argument(kind, n, n2, d):
+    torch.manual_seed(n * 3 + d)
+    x, y = torch.randn(n, d) * 0.6, torch.randn(n2, d) * 0.6
+    y[:5] = x[:5]
+    sc, var = _kernel_params(kind, d, -0.5, 0.2)
+    gk = torch.randn(n, n2)
+    ref_kind = "matern52_safe" if kind == "matern52" else kind
+    xr, yr, scr, varr = (t.double().requires_grad_(True) for t in (x, y, sc, var))
+    gp_ref.KERNELS[ref_kind](xr, yr, scr, varr).backward(gk.double())
+    xd, yd, scd, vard = (t.to(DEV).requires_grad_(True) for t in (x, y, sc, var))
+    ops.gram(kind, xd, yd, scd, vard).backward(gk.to(DEV))
+    assert rel_err(xd.grad, xr.grad) < 1e-3
+    assert rel_err(yd.grad, yr.grad) < 1e-3
+    assert rel_err(scd.grad, scr.grad) < 1e-3
+    assert rel_err(vard.grad, varr.grad) < 1e-3
+
+
+@pytest.mark.parametrize("kind", ["rbf", "matern52"])
+def test_gram_backward_same_argument(kind):
+    torch.manual_seed(5)
+    n, d = 140, 64
+    x = torch.randn(n, d) * 0.6
+    x[7] = x[3]
+    sc, var = _kernel_params(kind, d, -0.5, 0.2)
+    gk = torch.randn(n, n)
+    ref_kind = "matern52_safe" if kind == "matern52" else kind
+    xr, scr, varr = (t.double().requires_grad_(True) for t in (x, sc, var))
+    gp_ref.KERNELS[ref_kind](xr, xr, scr, varr).backward(gk.double())
+    xd, scd, vard = (t.to(DEV).requires_grad_(True) for t in (x, sc, var))
+    ops.gram(kind, xd, None, scd, vard).backward(gk.to(DEV))
+    assert rel_err(xd.grad, xr.grad) < 1e-3
+    assert rel_err(scd.grad, scr.grad) < 1e-3 and rel_err(vard.grad, varr.grad) < 1e-3
+    assert torch.isfinite(xd.grad).all()
+
+
+# ---------------------------------------------------------------------------------------------
+# kernel (4)
+# ---------------------------------------------------------------------------------------------
+def _spd(n, seed, cond_shift=0.5):
+    g = torch.Generator().manual_seed(seed)
+    a = torch.randn(n, n, generator=g, dtype=torch.float64)
+    return (a @ a.t() / n + cond_shift * torch.eye(n, dtype=torch.float64))
+
+
+@pytest.mark.parametrize("n,r", [(64, 0), (65, 3), (200, 17), (513, 300), (1000, 1), (1, 1), (130, 0)])
+def test_potrf_ext_sweep(n, r):
+    k = _spd(n, n)
+    b = torch.randn(r, n, dtype=torch.float64)
+    ld = ops._pad4(n)
+    e = torch.zeros(n + r, ld, device=DEV)
+    e[:n, :n] = k.float().to(DEV)
+    e[n:, :n] = b.float().to(DEV)
+    diag, info = ops.potrf_ext_raw(e, n, n_ext_dense=r)
+    assert int(info.item()) == 0
+    l_want = torch.linalg.cholesky(k)
+    l_got = torch.tril(e[:n, :n]).cpu()
+    assert rel_err(l_got, l_want) < 1e-5
+    assert rel_err(diag, torch.diagonal(l_want)) < 1e-5
+    if r:
+        x_want = torch.linalg.solve_triangular(l_want, b.t(), upper=False).t()   # B L^-T
+        assert rel_err(e[n:, :n], x_want) < 1e-4
+
+
+@pytest.mark.parametrize("n", [64, 100, 300])
+def test_potrf_ext_identity_rows_give_inverse_transpose(n):
+    k = _spd(n, 7 * n)
+    y = torch.randn(n, dtype=torch.float64)
+    ld = ops._pad4(n)
+    e = torch.zeros(2 * n + 1, ld, device=DEV)
+    e[:n, :n] = k.float().to(DEV)
+    e[n, :n] = y.float().to(DEV)
+    e[n + 1:, :n].diagonal().fill_(1.0)
+    ops.potrf_ext_raw(e, n, n_ext_dense=1, ext_identity=True)
+    l = torch.linalg.cholesky(k)
+    linv_t = torch.linalg.inv(l).t()
+    got = e[n + 1:, :n].cpu()
+    assert rel_err(got, linv_t) < 1e-4
+    assert torch.count_nonzero(torch.tril(got, -1)) == 0, "L^-T must stay exactly upper triangular"
+    assert rel_err(e[n, :n], torch.linalg.solve_triangular(l, y[:, None], upper=False).flatten()) < 1e-4
+
+
+def test_potrf_reports_non_positive_definite_like_torch():
+    n = 150
+    k = _spd(n, 3).float()
+    k[100, 100] = -1.0
+    e = k.to(DEV).clone()
+    with pytest.raises(RuntimeError, match="not positive-definite"):
+        ops.potrf_ext_raw(e, n)
+    e = k.to(DEV).clone()
+    _, info = ops.potrf_ext_raw(e, n, check=False)
+    assert int(info.item()) == 101      # LAPACK convention: order of the failing leading minor
+
+
+@pytest.mark.parametrize("n,r", [(70, 5), (300, 64)])
+def test_trsm_rlt(n, r):
+    l = torch.linalg.cholesky(_spd(n, n + 1))
+    b = torch.randn(r, n, dtype=torch.float64)
+    ld, xd = l.float().to(DEV).contiguous(), b.float().to(DEV).contiguous()
+    pb._lib.call("trsm_rlt", ld.data_ptr(), n, n, xd.data_ptr(), n, r)
+    want = torch.linalg.solve_triangular(l, b.t(), upper=False).t()
+    assert rel_err(xd, want) < 1e-4
+
+
+@pytest.mark.parametrize("n,r", [(90, 4), (200, 33)])
+def test_chol_solve_autograd(n, r):
+    torch.manual_seed(n)
+    k = _spd(n, n + 5)
+    b = torch.randn(n, r, dtype=torch.float64)
+    gl = torch.tril(torch.randn(n, n, dtype=torch.float64))
+    gx = torch.randn(n, r, dtype=torch.float64)
+    kr, br = k.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    lr = torch.linalg.cholesky(kr)
+    xr = torch.linalg.solve_triangular(lr, br, upper=False)
+    ((lr * gl).sum() + (xr * gx).sum()).backward()
+    kd, bd = k.float().to(DEV).requires_grad_(True), b.float().to(DEV).requires_grad_(True)
+    l, x = ops.chol_solve(kd, bd)
+    assert rel_err(l, lr) < 1e-5 and rel_err(x, xr) < 1e-4
+    assert torch.count_nonzero(torch.triu(l, 1)) == 0
+    ((l * gl.float().to(DEV)).sum() + (x * gx.float().to(DEV)).sum()).backward()
+    kg = 0.5 * (kr.grad + kr.grad.t())
+    assert rel_err(kd.grad, kg) < 2e-3
+    assert rel_err(bd.grad, br.grad) < 1e-3
+
+
+@pytest.mark.parametrize("kind", ["rbf", "matern52"])
+@pytest.mark.parametrize("logdet", ["trace", "exact"])
+@pytest.mark.parametrize("n,d", [(257, 32), (64, 128), (700, 128)])
+def test_exact_gp_loss_and_gradients(kind, logdet, n, d):
+    torch.manual_seed(n + d)
+    x = torch.randn(n, d) * 0.5
+    y = torch.randn(n, 1)
+    sc, var = _kernel_params(kind, d, -0.5, 0.3)
+    ls = torch.tensor(-2.0)
+    ref_kind = "matern52_safe" if kind == "matern52" else kind
+    xr, yr, scr, varr, lsr = (t.double().requires_grad_(True) for t in (x, y, sc, var, ls))
+    want = gp_ref.exact_gp_loss(xr, yr, scr, varr, lsr, kernel=ref_kind, logdet=logdet)
+    want.sum().backward()
+    want32 = gp_ref.exact_gp_loss(x, y, sc, var, ls, kernel=kind, logdet=logdet)
+    xd, yd, scd, vard, lsd = (t.to(DEV).requires_grad_(True) for t in (x, y, sc, var, ls))
+    got = ops.exact_gp_loss(xd, yd, scd, vard, lsd, kind=kind, exact_logdet=(logdet == "exact"))
+    assert got.shape == (1, 1)
+    assert rel_err(got, want) < 1e-5, "NLL within 1e-3 absolute is the bar; fp32 reaches 1e-5 relative"
+    assert abs(float(got) - float(want32)) < 1e-3 * max(1.0, abs(float(want32)))
+    (3.0 * got.sum()).backward()
+    for a, b_, name in [(xd, xr, "x"), (yd, yr, "y"), (scd, scr, "scale"), (vard, varr, "variance"), (lsd, lsr, "log_sigma")]:
+        assert rel_err(a.grad, 3.0 * b_.grad) < 2e-3, name
+
+
+@pytest.mark.parametrize("kind", ["rbf", "matern52"])
+@pytest.mark.parametrize("n,nte,d", [(300, 50, 32), (129, 7, 128), (64, 1, 16)])
+def test_exact_gp_posterior(kind, n, nte, d):
+    torch.manual_seed(n + nte)
+    x, xt = torch.randn(n, d) * 0.5, torch.randn(nte, d) * 0.5
+    xt[0] = x[0]   # a test point equal to a training point
+    y = torch.randn(n, 1)
+    sc, var = _kernel_params(kind, d, -0.5, 0.3)
+    ls = torch.tensor(-2.0)
+    mean_w, cov_w = gp_ref.exact_gp_condition(xt.double(), x.double(), y.double(), sc.double(), var.double(),
+                                              ls.double(), kernel=kind)
+    args = [t.to(DEV) for t in (xt, x, y, sc, var, ls)]
+    mean, cov = ops.exact_gp_posterior(*args, kind=kind, full_cov=True)
+    assert rel_err(mean, mean_w) < 1e-4 and rel_err(cov, cov_w) < 1e-4
+    mean2, v = ops.exact_gp_posterior(*args, kind=kind, full_cov=False)
+    assert rel_err(mean2, mean_w) < 1e-4
+    assert max_rel_err(v, torch.diagonal(cov_w), floor=1e-3) < 1e-3
