@@ -43,7 +43,8 @@ def test_aggregate_fwd_bwd(feat, norm):
     got = ops.aggregate(xd, gd.csr(), norm)
     got.backward(go.to(DEV))
     assert rel_err(got, want) < 1e-6
-    assert max_rel_err(got, want) < 1e-4
+    # element-wise: sums of +-O(1) terms cancel, so the floor is 1e-3 of the largest entry
+    assert max_rel_err(got, want, floor=1e-3) < 1e-4
     assert rel_err(xd.grad, xr.grad) < 1e-6
 
 
