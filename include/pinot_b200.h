@@ -128,6 +128,29 @@ PINOT_B200_API int pinot_b200_gram_bwd(int kind, const float* x, const float* y,
 PINOT_B200_API int64_t pinot_b200_potrf_workspace_bytes(int64_t n);
 PINOT_B200_API int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, int ext_identity,
                          float* diag_out, void* workspace, int* info, cudaStream_t stream);
+/* The same sweep as pinot_b200_potrf_ext for callers that cannot hand over scratch memory.
+ * (No counterpart in the reference: pinot lets torch allocate whatever cuSOLVER asks for.)
+ *
+ * Who needs it: code that receives device buffers from a host framework but has no way to obtain
+ * more -- e.g. a plug-in running inside a runtime whose memory pool owns the whole GPU -- and loops
+ * that must not call cudaMalloc because it synchronises the device.  The deferred diagonal blocks
+ * are kept in an array compiled into the library (2 MiB of device memory per GPU that loads it,
+ * held until the process exits), so no workspace argument exists and nothing is allocated or
+ * freed, here or in any routine it calls.  Inputs and outputs (e, diag_out, info) are still the
+ * caller's.
+ *
+ * Limits and rules:
+ *   - n <= PINOT_B200_POTRF_NOALLOC_MAX_N; larger n returns code 3 with a message naming the limit;
+ *   - the first call on each device looks up the array's device address (once, cached); make that
+ *     first call before starting any stream capture on that device;
+ *   - every call on a device uses the same array: two calls that may overlap on the GPU (different
+ *     streams, or different host threads) race with each other -- serialise them.  Back-to-back
+ *     calls on one stream are fine; nothing needs clearing in between because each call overwrites
+ *     every scratch entry before reading it. */
+#define PINOT_B200_POTRF_NOALLOC_MAX_N 8192
+PINOT_B200_API int pinot_b200_potrf_ext_noalloc(float* e, int64_t ld, int64_t n, int64_t n_ext_dense,
+                                                int ext_identity, float* diag_out, int* info,
+                                                cudaStream_t stream);
 /* X (r x n) <- X L^{-T} for an already factored lower-triangular L (torch.triangular_solve(
  * input=X^T, A=L, upper=False) transposed; gaussian_process_regressor.py:112-114,215,376-390). */
 PINOT_B200_API int pinot_b200_trsm_rlt(const float* l, int64_t ldl, int64_t n, float* x, int64_t ldx, int64_t r,

@@ -33,6 +33,7 @@ SIGNATURES = {
     "pinot_b200_gram_bwd": [_i32, _ptr, _ptr, _ptr, _i64, _ptr, _ptr, _i64, _i64, _i64, _i64, _ptr, _ptr, _ptr, _ptr, _i32, _ptr],
     "pinot_b200_potrf_workspace_bytes": [_i64],
     "pinot_b200_potrf_ext": [_ptr, _i64, _i64, _i64, _i32, _ptr, _ptr, _ptr, _ptr],
+    "pinot_b200_potrf_ext_noalloc": [_ptr, _i64, _i64, _i64, _i32, _ptr, _ptr, _ptr],
     "pinot_b200_trsm_rlt": [_ptr, _i64, _i64, _ptr, _i64, _i64, _ptr],
     "pinot_b200_zero_upper": [_ptr, _i64, _i64, _ptr],
     "pinot_b200_gemv_rows": [_ptr, _i64, _i64, _i64, _i32, _ptr, _ptr, _ptr],

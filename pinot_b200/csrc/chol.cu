@@ -16,6 +16,7 @@
 #include "gemm.cuh"
 #include "../../include/pinot_b200.h"
 #include <math.h>
+#include <mutex>
 
 namespace {
 
@@ -318,6 +319,90 @@ int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, i
     }
     chol_writeback_kernel<<<(unsigned)pb::ceil_div(n, NB), 256, 0, stream>>>(e, ld, (int)n, wdiag, diag_out);
     return pb::check_launch("chol_writeback");
+}
+
+// ---------------------------------------------------------------------------------------------
+// Sweep with built-in scratch.
+//
+// Some hosts of this library may not allocate device memory at the moment they need a
+// factorisation: a plug-in that is handed raw tensors by a framework which owns the whole GPU
+// through its own memory pool and exposes no allocator to foreign code; a serving loop that must
+// not call cudaMalloc because that call synchronises the device and stalls every other stream.
+// For them the deferred diagonal blocks of the sweep live in this file-scope device array instead
+// of a caller-provided workspace.  It costs PINOT_B200_POTRF_NOALLOC_MAX_N * 64 * 4 bytes (2 MiB) of
+// device memory on every GPU that loads the library, for the life of the process.
+// ---------------------------------------------------------------------------------------------
+constexpr int64_t kNoAllocMaxN = PINOT_B200_POTRF_NOALLOC_MAX_N;
+static_assert(kNoAllocMaxN % NB == 0, "the limit must be a whole number of panels");
+static __device__ __align__(256) float g_noalloc_diag_scratch[(kNoAllocMaxN / NB) * NB * NB];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mu;
+float* g_noalloc_ptr[kMaxDevices] = {nullptr};
+
+// The array's name is only a host-side handle; kernels need its device address, which differs per
+// GPU.  Looked up once per device, with that device current, and cached.
+int noalloc_scratch_for_current_device(float** out) {
+    int dev = -1;
+    PB_CUDA(cudaGetDevice(&dev));
+    PB_REQUIRE(dev >= 0 && dev < kMaxDevices, "potrf_ext_noalloc: device ordinal %d not supported", dev);
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (g_noalloc_ptr[dev] == nullptr) {
+        float* p = nullptr;
+        cudaError_t err = cudaGetSymbolAddress((void**)&p, g_noalloc_diag_scratch);
+        if (err != cudaSuccess || p == nullptr) {
+            pb::set_error("potrf_ext_noalloc: cudaGetSymbolAddress failed on device %d: %d (%s)", dev, (int)err,
+                          cudaGetErrorString(err));
+            return pb::PB_ERR_CUDA;
+        }
+        g_noalloc_ptr[dev] = p;
+    }
+    *out = g_noalloc_ptr[dev];
+    return pb::PB_OK;
+}
+}  // namespace
+
+int pinot_b200_potrf_ext_noalloc(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, int ext_identity,
+                                 float* diag_out, int* info, cudaStream_t stream) {
+    PB_REQUIRE(n >= 0 && n_ext_dense >= 0 && ld >= n, "potrf_ext_noalloc: invalid sizes");
+    PB_REQUIRE(info, "potrf_ext_noalloc: info pointer is required");
+    if (n > kNoAllocMaxN) {
+        pb::set_error("potrf_ext_noalloc: n = %lld exceeds the built-in scratch limit of %lld rows; call "
+                      "pinot_b200_potrf_ext with a caller-provided workspace instead",
+                      (long long)n, (long long)kNoAllocMaxN);
+        return pb::PB_ERR_LIMIT;
+    }
+    float* wdiag = nullptr;
+    int rc = noalloc_scratch_for_current_device(&wdiag);
+    if (rc) return rc;
+    PB_CUDA(cudaMemsetAsync(info, 0, sizeof(int), stream));
+    if (n == 0) return pb::PB_OK;
+    PB_REQUIRE(e, "potrf_ext_noalloc: null pointer");
+    // Nothing in the scratch has to start at zero: the panel step of column block b writes all
+    // 64 x 64 entries of slot b before the final write-back reads them, so whatever an earlier
+    // call left behind is never observed.
+    const int64_t r_total = n_ext_dense + (ext_identity ? n : 0);
+    for (int64_t c0 = 0; c0 < n; c0 += NB) {
+        const int nb = (int)((n - c0) < NB ? (n - c0) : NB);
+        const int64_t c1 = c0 + nb;
+        const int64_t r_act = ext_identity ? (n_ext_dense + c1) : r_total;
+        const int64_t row_end = n + r_act;
+        rc = launch_panel(e, ld, e, ld, (int)c0, nb, c1, row_end, 0, wdiag + (c0 / NB) * NB * NB, info, stream);
+        if (rc) return rc;
+        if (c1 < n) {
+            pb::GemmParams g;
+            g.M = (int)(row_end - c1); g.N = (int)(n - c1); g.K = nb;
+            g.A = e + c1 * ld + c0; g.lda = ld; g.transA = false;
+            g.B = e + c1 * ld + c0; g.ldb = ld; g.transB = true;
+            g.C = e + c1 * ld + c1; g.ldc = ld;
+            g.alpha = -1.f; g.beta = 1.f; g.lower = 1;
+            rc = pb::gemm(g, stream);
+            if (rc) return rc;
+        }
+    }
+    chol_writeback_kernel<<<(unsigned)pb::ceil_div(n, NB), 256, 0, stream>>>(e, ld, (int)n, wdiag, diag_out);
+    return pb::check_launch("chol_writeback (noalloc)");
 }
 
 int pinot_b200_trsm_rlt(const float* l, int64_t ldl, int64_t n, float* x, int64_t ldx, int64_t r,
