@@ -14,6 +14,8 @@
 // V^T = K_te,tr L^{-T} (all that the predictive distribution needs).  Identity extension rows are
 // only touched from the column block where their 1 sits, so L^{-T} costs n^3/3 extra flops.
 #include "gemm.cuh"
+#include "chol_diag.cuh"
+#include <stdlib.h>
 #include "../../include/pinot_b200.h"
 #include <math.h>
 #include <mutex>
@@ -28,7 +30,7 @@ constexpr int LDT = NB + 1;   // shared stride of the staged panel rows
 // Factor the nb x nb diagonal block held (unfactored, lower part valid) in Ls.  On exit the lower
 // triangle of Ls holds L11 and invd[j] = 1 / L11[j][j].  Returns the first failing pivot (0-based)
 // or -1.  All 256 threads take part.
-__device__ int factor_diag_block(float* __restrict__ Ls, float* __restrict__ dj, int nb) {
+__device__ int factor_diag_block(float* Ls, float* dj, int nb) {
     const int tid = threadIdx.x;
     const int ti = tid >> 4, tc = tid & 15;
     int fail = -1;
@@ -268,6 +270,24 @@ gp_predict_kernel(const float* __restrict__ Vt, int64_t ld, int64_t n_te, int64_
     }
 }
 
+// Stand-alone factorisation of one diagonal block (first block of a sweep, or every block when the
+// look-ahead is switched off): L11 -> wdiag, L11^{-T} -> winv.
+__global__ void __launch_bounds__(256)
+chol_diag_kernel(const float* __restrict__ E, int64_t ld, int c0, int nb, float* __restrict__ wdiag,
+                 float* __restrict__ winv, int* __restrict__ info) {
+    __shared__ __align__(16) float S[pb::DIAG_SMEM_FLOATS];
+    const int fail = pb::factor_diag_block_regs(E, ld, c0, nb, /*coherent=*/false, S, wdiag, winv);
+    if (fail >= 0 && threadIdx.x == 0) atomicCAS(info, 0, c0 + fail + 1);
+}
+
+bool lookahead_enabled() {
+    static const bool on = [] {
+        const char* v = getenv("PINOT_B200_LOOKAHEAD");
+        return !(v && v[0] == '0');
+    }();
+    return on;
+}
+
 size_t panel_smem_bytes() { return sizeof(float) * (size_t)(NB * LDL + NB + PR * LDT); }
 
 int launch_panel(const float* D, int64_t ldd, float* P, int64_t ldp, int c0, int nb, int64_t row_beg,
@@ -287,7 +307,8 @@ extern "C" {
 
 int64_t pinot_b200_potrf_workspace_bytes(int64_t n) {
     if (n < 0) return -1;
-    return (int64_t)sizeof(float) * pb::ceil_div(n, NB) * NB * NB;
+    // per column block: L11 (deferred diagonal write-back) and L11^{-T} (panel TRSM as a GEMM)
+    return (int64_t)sizeof(float) * pb::ceil_div(n, NB) * NB * NB * 2;
 }
 
 int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, int ext_identity,
@@ -297,15 +318,36 @@ int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, i
     PB_CUDA(cudaMemsetAsync(info, 0, sizeof(int), stream));
     if (n == 0) return pb::PB_OK;
     PB_REQUIRE(e && workspace, "potrf_ext: null pointer");
+    const int64_t nblk = pb::ceil_div(n, NB);
     float* wdiag = static_cast<float*>(workspace);
+    float* winv = wdiag + nblk * NB * NB;
     const int64_t r_total = n_ext_dense + (ext_identity ? n : 0);
+    const bool lookahead = lookahead_enabled();
+    // Per column block [c0, c1):
+    //   (a) the diagonal block's factor L11 and M = L11^{-T} are in the workspace (first block: a
+    //       one-CTA kernel; later blocks: produced by tile (0,0) of the previous trailing update
+    //       while the other tiles are still being computed);
+    //   (b) panel "TRSM" as a GEMM: rows below the block and the active extension rows *= M;
+    //   (c) rank-nb trailing update of everything to the right (lower triangle + extension rows).
     for (int64_t c0 = 0; c0 < n; c0 += NB) {
         const int nb = (int)((n - c0) < NB ? (n - c0) : NB);
-        const int64_t c1 = c0 + nb;
+        const int64_t c1 = c0 + nb, b = c0 / NB;
         const int64_t r_act = ext_identity ? (n_ext_dense + c1) : r_total;
-        const int64_t row_beg = c1, row_end = n + r_act;
-        int rc = launch_panel(e, ld, e, ld, (int)c0, nb, row_beg, row_end, 0, wdiag + (c0 / NB) * NB * NB, info, stream);
-        if (rc) return rc;
+        const int64_t row_end = n + r_act;
+        if (c0 == 0 || !lookahead) {
+            chol_diag_kernel<<<1, 256, 0, stream>>>(e, ld, (int)c0, nb, wdiag + b * NB * NB, winv + b * NB * NB, info);
+            int rc = pb::check_launch("chol_diag");
+            if (rc) return rc;
+        }
+        if (row_end > c1) {
+            pb::GemmParams g;   // in place: every CTA owns whole rows of the panel (N = nb <= one tile)
+            g.M = (int)(row_end - c1); g.N = nb; g.K = nb;
+            g.A = e + c1 * ld + c0; g.lda = ld;
+            g.B = winv + b * NB * NB; g.ldb = NB;
+            g.C = e + c1 * ld + c0; g.ldc = ld;
+            int rc = pb::gemm(g, stream);
+            if (rc) return rc;
+        }
         if (c1 < n) {
             pb::GemmParams g;
             g.M = (int)(row_end - c1); g.N = (int)(n - c1); g.K = nb;
@@ -313,11 +355,18 @@ int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, i
             g.B = e + c1 * ld + c0; g.ldb = ld; g.transB = true;
             g.C = e + c1 * ld + c1; g.ldc = ld;
             g.alpha = -1.f; g.beta = 1.f; g.lower = 1;
-            rc = pb::gemm(g, stream);
+            if (lookahead) {
+                g.post_wdiag = wdiag + (b + 1) * NB * NB;
+                g.post_winv = winv + (b + 1) * NB * NB;
+                g.post_info = info;
+                g.post_nb = (int)((n - c1) < NB ? (n - c1) : NB);
+                g.post_c0 = (int)c1;
+            }
+            int rc = pb::gemm(g, stream);
             if (rc) return rc;
         }
     }
-    chol_writeback_kernel<<<(unsigned)pb::ceil_div(n, NB), 256, 0, stream>>>(e, ld, (int)n, wdiag, diag_out);
+    chol_writeback_kernel<<<(unsigned)nblk, 256, 0, stream>>>(e, ld, (int)n, wdiag, diag_out);
     return pb::check_launch("chol_writeback");
 }
 

@@ -1,0 +1,107 @@
+// In-CTA factorisation of one 64x64 diagonal block of the Cholesky sweep, together with the
+// transposed inverse of its factor.  Shared by the stand-alone diagonal kernel (chol.cu) and by the
+// look-ahead epilogue of the trailing-update GEMMs (gemm.cu, gemm_tc.cu).
+//
+// The block is factored "augmented": rows 0..63 are the block A11, rows 64..127 an identity.
+// Right-looking elimination of the stacked (128 x 64) matrix gives [ L11 ; L11^{-T} ] -- the same
+// trick the sweep itself plays with its extension rows -- so the panel TRSM that follows becomes a
+// plain GEMM with M = L11^{-T}.
+//
+// Mapping: thread r (r < 128) keeps row r of the stacked matrix in 64 registers.  Step j:
+//   every thread scales its column-j entry by 1/sqrt(pivot) and publishes it (transposed) to shared
+//   memory; after one barrier each thread applies the rank-1 update to its remaining entries with
+//   63-j independent FMAs fed by broadcast LDS.128 reads.  Two barriers per step, no divergence,
+//   ~2000 FMAs per thread in total: a few microseconds instead of the tens a shared-memory
+//   read-modify-write formulation needs.
+#pragma once
+#include "common.cuh"
+
+namespace pb {
+
+constexpr int DIAG_NB = 64;                 // panel width
+constexpr int DIAG_LT = DIAG_NB;            // Lt[j][c] = column j of the stacked factor, c < 64 (A rows only)
+constexpr int DIAG_SMEM_FLOATS = DIAG_NB * DIAG_LT + DIAG_NB;   // Lt + pivots
+
+// Factor the nb x nb block at (c0, c0) of `src` (lower triangle read) and write L11 (zero above the
+// diagonal) to wdiag and M = L11^{-T} (zero below it) to winv, both dense 64 x 64 (identity
+// padding beyond nb).  smem: DIAG_SMEM_FLOATS floats.  All threads of the CTA must call this
+// (blockDim.x >= 128); threads >= 128 only take part in the barriers.  `coherent` avoids the
+// read-only path (the look-ahead epilogue reads values the same CTA has just written).
+// Returns the first failing pivot (0-based) or -1 (same value in every thread).
+__device__ __forceinline__ int factor_diag_block_regs(const float* src, int64_t ld, int c0, int nb, bool coherent,
+                                                      float* smem, float* __restrict__ wdiag,
+                                                      float* __restrict__ winv) {
+    // NB `smem` must NOT be __restrict__: it carries data between threads across the barriers, and a
+    // restrict-qualified pointer lets the compiler hoist those loads above __syncthreads().
+    float* Lt = smem;                       // [64][64]: Lt[j][c] = L[c][j]
+    float* piv = smem + DIAG_NB * DIAG_LT;  // [64]
+    const int tid = threadIdx.x;
+    const bool active = tid < 2 * DIAG_NB;
+    const bool is_a = tid < DIAG_NB;        // rows of A11; the rest are identity rows
+    const int r = is_a ? tid : tid - DIAG_NB;
+
+    float a[DIAG_NB];
+#pragma unroll
+    for (int c = 0; c < DIAG_NB; ++c) a[c] = 0.f;
+    if (active) {
+        if (is_a && r < nb) {
+            const float* row = src + (int64_t)(c0 + r) * ld + c0;
+            const bool vec = ((ld & 3) == 0) && ((reinterpret_cast<uintptr_t>(row) & 15u) == 0) && (nb == DIAG_NB);
+            if (vec) {
+#pragma unroll
+                for (int c = 0; c < DIAG_NB; c += 4) {
+                    const float4 v = coherent ? __ldcv(reinterpret_cast<const float4*>(row + c))
+                                              : __ldg(reinterpret_cast<const float4*>(row + c));
+                    a[c] = v.x; a[c + 1] = v.y; a[c + 2] = v.z; a[c + 3] = v.w;
+                }
+#pragma unroll
+                for (int c = 0; c < DIAG_NB; ++c)
+                    if (c > r) a[c] = 0.f;                                  // only the lower triangle is valid
+            } else {
+#pragma unroll
+                for (int c = 0; c < DIAG_NB; ++c)
+                    if (c <= r) a[c] = coherent ? __ldcv(row + c) : __ldg(row + c);
+            }
+        } else {
+#pragma unroll
+            for (int c = 0; c < DIAG_NB; ++c) a[c] = (c == r) ? 1.f : 0.f;   // identity rows / padding
+        }
+    }
+    int fail = -1;
+#pragma unroll
+    for (int j = 0; j < DIAG_NB; ++j) {
+        // pivot: thread j owns S[j][j]
+        if (tid == j) piv[j] = a[j];
+        __syncthreads();
+        float d = piv[j];
+        if (!(d > 0.f)) {   // also catches NaN
+            if (fail < 0 && j < nb) fail = j;
+            d = 1.f;
+        }
+        const float inv = 1.f / sqrtf(d);
+        a[j] *= inv;                               // L[r][j] (thread j: sqrt(d)), or M[r][j]
+        if (is_a) Lt[j * DIAG_LT + tid] = a[j];    // publish column j of L (rows of A11 only)
+        __syncthreads();
+        if (active && j + 1 < DIAG_NB) {
+            const float x = a[j];
+#pragma unroll
+            for (int c = j + 1; c < DIAG_NB; ++c) a[c] = fmaf(-x, Lt[j * DIAG_LT + c], a[c]);
+        }
+    }
+    // results: thread r < 64 holds row r of L11 (entries c <= r), thread 64 + r row r of M (c >= r)
+    if (active) {
+        float* dst = (is_a ? wdiag : winv) + r * DIAG_NB;
+#pragma unroll
+        for (int c = 0; c < DIAG_NB; c += 4) {
+            float4 v;
+            v.x = (is_a ? (c + 0 <= r) : (c + 0 >= r)) ? a[c + 0] : 0.f;
+            v.y = (is_a ? (c + 1 <= r) : (c + 1 >= r)) ? a[c + 1] : 0.f;
+            v.z = (is_a ? (c + 2 <= r) : (c + 2 >= r)) ? a[c + 2] : 0.f;
+            v.w = (is_a ? (c + 3 <= r) : (c + 3 >= r)) ? a[c + 3] : 0.f;
+            *reinterpret_cast<float4*>(dst + c) = v;
+        }
+    }
+    return fail;
+}
+
+}  // namespace pb

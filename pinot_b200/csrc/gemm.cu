@@ -7,7 +7,9 @@
 // single-pass TF32/BF16 tensor-core products ("hard parts").
 // Tile 128x128x16, 256 threads, 8x8 outputs per thread split in two 4-wide halves so that every
 // shared-memory fragment read is a conflict-free (or broadcast) LDS.128.
-#include "gemm.cuh"
+#include "gemm_params.cuh"
+#include "chol_diag.cuh"
+#include <stdlib.h>
 #include "../../include/pinot_b200.h"
 
 namespace pb {
@@ -16,20 +18,8 @@ namespace {
 
 constexpr int BM = 128, BN = 128, BK = 16, PAD = 4, NT = 256;
 
-struct KParams {
-    int M, N, K;
-    const float* A; int64_t lda;
-    const float* B; int64_t ldb;
-    float* C; int64_t ldc;
-    float alpha, beta;
-    const float* alpha_dev;
-    const float* bias;
-    int act;
-    const float* kscale;
-    const float* r1u; const float* r1v; float r1coef;
-    int lower, mirror, ktri, splitk;
-    int vecA, vecB, vecC;
-};
+constexpr int TILE_FLOATS = 2 * BK * (BM + PAD);   // one operand, both pipeline stages
+constexpr int SMEM_FLOATS = (2 * TILE_FLOATS > DIAG_SMEM_FLOATS) ? 2 * TILE_FLOATS : DIAG_SMEM_FLOATS;
 
 // Tile of a matrix stored [row][k] (k contiguous): thread -> (row = tid/4 + 64*i, k = (tid%4)*4..+3)
 __device__ __forceinline__ void load_kcontig(const float* __restrict__ P, int64_t ld, int rows, int kend,
@@ -116,8 +106,10 @@ __device__ __forceinline__ void store_rowcontig(float (*S)[BM + PAD], const floa
 
 template <bool TA, bool TB>
 __global__ void __launch_bounds__(NT, 2) sgemm_kernel(const KParams p) {
-    __shared__ __align__(16) float As[2][BK][BM + PAD];
-    __shared__ __align__(16) float Bs[2][BK][BN + PAD];
+    // one buffer: the A/B pipeline stages, reused by the look-ahead factorisation after the epilogue
+    __shared__ __align__(16) float smem_all[SMEM_FLOATS];
+    float (*As)[BK][BM + PAD] = reinterpret_cast<float (*)[BK][BM + PAD]>(smem_all);
+    float (*Bs)[BK][BN + PAD] = reinterpret_cast<float (*)[BK][BN + PAD]>(smem_all + TILE_FLOATS);
 
     const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
     if (p.lower && n0 > m0 + BM - 1) return;
@@ -243,9 +235,26 @@ __global__ void __launch_bounds__(NT, 2) sgemm_kernel(const KParams p) {
             }
         }
     }
+
+    // ---------------- Cholesky look-ahead (tile (0,0) only) ----------------
+    if (p.post_wdiag != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {
+        __syncthreads();   // this CTA's stores to C are visible to all of its threads
+        const int fail = factor_diag_block_regs(p.C, p.ldc, 0, p.post_nb, /*coherent=*/true, smem_all,
+                                                p.post_wdiag, p.post_winv);
+        if (fail >= 0 && threadIdx.x == 0 && p.post_info) atomicCAS(p.post_info, 0, p.post_c0 + fail + 1);
+    }
 }
 
 }  // namespace
+
+// PINOT_B200_GEMM=ffma selects the CUDA-core kernel; the default is the tcgen05 3xTF32 kernel.
+static bool use_tensor_cores() {
+    static const bool on = [] {
+        const char* v = getenv("PINOT_B200_GEMM");
+        return !(v && (v[0] == 'f' || v[0] == 'F'));
+    }();
+    return on;
+}
 
 int gemm(const GemmParams& g, cudaStream_t stream) {
     PB_REQUIRE(g.M >= 0 && g.N >= 0 && g.K >= 0, "gemm: negative size");
@@ -262,6 +271,10 @@ int gemm(const GemmParams& g, cudaStream_t stream) {
     p.vecA = aligned16(g.A) && (g.lda % 4 == 0);
     p.vecB = aligned16(g.B) && (g.ldb % 4 == 0);
     p.vecC = aligned16(g.C) && (g.ldc % 4 == 0);
+    p.post_wdiag = g.post_wdiag; p.post_winv = g.post_winv; p.post_info = g.post_info;
+    p.post_nb = g.post_nb; p.post_c0 = g.post_c0;
+    PB_REQUIRE(!g.post_wdiag || (g.post_winv && g.splitk == 1 && g.post_nb > 0 && g.post_nb <= DIAG_NB),
+               "gemm: invalid look-ahead parameters");
     if (g.splitk > 1) {
         PB_REQUIRE(g.beta == 0.f || g.beta == 1.f, "gemm: split-K needs beta in {0,1}");
         PB_REQUIRE(!g.bias && !g.act && !g.r1u && !g.mirror, "gemm: split-K supports a plain epilogue only");
@@ -275,6 +288,7 @@ int gemm(const GemmParams& g, cudaStream_t stream) {
     }
     dim3 grid((unsigned)ceil_div(g.N, BN), (unsigned)ceil_div(g.M, BM), (unsigned)g.splitk);
     PB_REQUIRE(grid.y <= 65535, "gemm: M too large for one launch (%d rows)", g.M);
+    if (use_tensor_cores()) return launch_gemm_tc(p, g.transA, g.transB, grid, stream);
     if (!g.transA && !g.transB) sgemm_kernel<false, false><<<grid, NT, 0, stream>>>(p);
     else if (!g.transA && g.transB) sgemm_kernel<false, true><<<grid, NT, 0, stream>>>(p);
     else if (g.transA && !g.transB) sgemm_kernel<true, false><<<grid, NT, 0, stream>>>(p);

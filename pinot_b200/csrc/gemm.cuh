@@ -25,6 +25,15 @@ struct GemmParams {
     int ktri = 0;    // 1: op(A)[m,k] == 0 for k < m (and op(B)[k,n] == 0 for k < n): skip k < tile row origin
     int splitk = 1;  // >1: K is split over grid.z and partial sums are atomically added into C
                      //     (beta must be 0 or 1; for 0 the caller's C is zeroed by gemm())
+    // Cholesky look-ahead: after storing its tile, the CTA that owns tile (0, 0) factors the
+    // post_nb x post_nb block at C's origin (the next diagonal block of the sweep) and writes
+    // L11 / L11^{-T} to post_wdiag / post_winv (64 x 64 floats each); a non-positive pivot sets
+    // *post_info to post_c0 + pivot + 1 (if still 0).
+    float* post_wdiag = nullptr;
+    float* post_winv = nullptr;
+    int* post_info = nullptr;
+    int post_nb = 0;
+    int post_c0 = 0;
 };
 
 // Launches the GEMM on `stream`.  Returns PB_OK or an error code (message via set_error).

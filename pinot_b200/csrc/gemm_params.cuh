@@ -1,0 +1,26 @@
+// Kernel-side parameter block shared by the FFMA GEMM (gemm.cu) and the tcgen05 GEMM (gemm_tc.cu).
+#pragma once
+#include "gemm.cuh"
+
+namespace pb {
+
+struct KParams {
+    int M, N, K;
+    const float* A; int64_t lda;
+    const float* B; int64_t ldb;
+    float* C; int64_t ldc;
+    float alpha, beta;
+    const float* alpha_dev;
+    const float* bias;
+    int act;
+    const float* kscale;
+    const float* r1u; const float* r1v; float r1coef;
+    int lower, mirror, ktri, splitk;
+    int vecA, vecB, vecC;
+    float* post_wdiag; float* post_winv; int* post_info; int post_nb, post_c0;
+};
+
+// gemm_tc.cu: 3xTF32 tensor-core (tcgen05 / TMEM) implementation of the same contract.
+int launch_gemm_tc(const KParams& p, bool transA, bool transB, dim3 grid, cudaStream_t stream);
+
+}  // namespace pb

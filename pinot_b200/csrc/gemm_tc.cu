@@ -1,0 +1,435 @@
+// Tensor-core implementation of the library's fp32 GEMM contract: tcgen05.mma (kind::tf32) with the
+// accumulator in TMEM, fp32 accuracy recovered by the 3xTF32 split
+//     a = a_hi + a_lo,  b = b_hi + b_lo   (each part exactly representable in TF32)
+//     a.b ~= a_hi.b_hi + a_hi.b_lo + a_lo.b_hi        (the dropped a_lo.b_lo term is ~2^-22 |a||b|)
+// so that the embedding / Cholesky parity bars (1e-4 relative) keep holding where a single TF32 or
+// BF16 pass would not.
+//
+// One CTA (256 threads) owns a 128 x 128 output tile:
+//   * all 8 warps stream op(A) / op(B) K-slabs (16 columns at a time) from global memory, split them
+//     and store hi / lo parts to shared memory in the canonical K-major, un-swizzled UMMA layout
+//     (8-row x 16-byte core matrices; SBO = 128 B between 8-row groups, LBO = 2080 B between
+//     K-adjacent core matrices -- the 32-byte pad keeps the coalesced stores bank-conflict free);
+//   * one thread issues the tcgen05.mma instructions (M = 128, N <= 128, K = 8 each, 3 per K-step)
+//     and commits them to an mbarrier per pipeline stage, which is what releases the stage's shared
+//     memory for the next slab (3-stage ring, loads of slab k+1 overlap the MMAs of slab k);
+//   * fp32 accumulation in TMEM truncates, so the error grows with the number of MMAs: the small cross
+//     terms get their own accumulator (TMEM columns 128-255) and both are flushed into C every 512
+//     K-columns, which bounds the accumulation error independently of K;
+//   * the epilogue reads the accumulator back with tcgen05.ld (each warp its 32 TMEM lanes, i.e. 32
+//     rows; warps 0-3 the left 64 columns, warps 4-7 the right ones) and applies the same fused
+//     epilogue as the FFMA kernel (alpha/beta, bias, tanh, rank-1 term, lower/mirror masks,
+//     split-K atomics, Cholesky look-ahead).
+#include "gemm_params.cuh"
+#include "chol_diag.cuh"
+
+namespace pb {
+
+namespace {
+
+constexpr int TM = 128, TN = 128, TK = 16;     // CTA tile; TK fp32 columns per pipeline stage
+constexpr int STAGES = 3;
+constexpr int NTHREADS = 256;
+constexpr int SBO_BYTES = 128;                 // between 8-row groups
+constexpr int LBO_BYTES = (TM / 8) * 128 + 32; // between K-adjacent core matrices (+32 B pad)
+constexpr int KC_PER_STAGE = TK / 4;           // 16-byte K chunks per stage
+constexpr int OPERAND_BYTES = KC_PER_STAGE * LBO_BYTES;          // one of A_hi, A_lo, B_hi, B_lo
+constexpr int STAGE_BYTES = 4 * OPERAND_BYTES;
+constexpr int PIPE_BYTES = STAGES * STAGE_BYTES;
+constexpr int DIAG_BYTES = DIAG_SMEM_FLOATS * 4;
+constexpr int DYN_SMEM_BYTES = (PIPE_BYTES > DIAG_BYTES ? PIPE_BYTES : DIAG_BYTES) + 128;
+constexpr int TMEM_COLS = 256;                // [0,128): hi.hi accumulator, [128,256): cross terms
+constexpr int KCHUNK = 512;                   // accumulator is flushed to C every KCHUNK columns
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    const uint32_t addr = smem_u32(bar);
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE;\n\t"
+        "bra WAIT_LOOP;\n\t"
+        "DONE:\n\t"
+        "}\n" ::"r"(addr), "r"(parity)
+        : "memory");
+}
+
+// 64-bit shared-memory matrix descriptor: K-major, SWIZZLE_NONE, version 1 (sm_100).
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3FFF);                    // start address      bits [0,14)
+    d |= (uint64_t)((LBO_BYTES >> 4) & 0x3FFF) << 16;          // leading byte off.  bits [16,30)
+    d |= (uint64_t)((SBO_BYTES >> 4) & 0x3FFF) << 32;          // stride byte off.   bits [32,46)
+    d |= (uint64_t)1 << 46;                                    // descriptor version bits [46,48)
+    return d;                                                  // layout type 0 = no swizzle
+}
+
+// Instruction descriptor: D = F32, A = B = TF32, both K-major, M = 128, N = n.
+__device__ __forceinline__ uint32_t make_idesc(int n) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+}
+
+__device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "}\n" ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void mma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+
+__device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
+    uint32_t h, l;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h) : "f"(x));
+    hi = __uint_as_float(h);
+    const float r = x - hi;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(l) : "f"(r));
+    lo = __uint_as_float(l);
+}
+
+// ---- operand staging -------------------------------------------------------------------------
+// Register image of one K-slab of one operand: 2 x float4 per thread.
+//   k-contiguous storage ([row][k]):   thread -> row = tid/4 + 64*i, kc = tid%4   (float4 along k)
+//   row-contiguous storage ([k][row]): thread -> k = tid/32 + 8*i, rows (tid%32)*4 .. +3
+__device__ __forceinline__ void tc_load_kcontig(const float* __restrict__ P, int64_t ld, int rows, int kend,
+                                                int row0, int k0, int vec, const float* __restrict__ kscale,
+                                                float4 (&r)[2]) {
+    const int tid = threadIdx.x;
+    const int k = k0 + (tid & 3) * 4;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int row = row0 + (tid >> 2) + 64 * i;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (row < rows && k < kend) {
+            const float* src = P + (int64_t)row * ld + k;
+            if (vec && k + 3 < kend) {
+                v = ldg4(src);
+            } else {
+                v.x = __ldg(src);
+                if (k + 1 < kend) v.y = __ldg(src + 1);
+                if (k + 2 < kend) v.z = __ldg(src + 2);
+                if (k + 3 < kend) v.w = __ldg(src + 3);
+            }
+            if (kscale) {
+                v.x *= __ldg(kscale + k);
+                if (k + 1 < kend) v.y *= __ldg(kscale + k + 1);
+                if (k + 2 < kend) v.z *= __ldg(kscale + k + 2);
+                if (k + 3 < kend) v.w *= __ldg(kscale + k + 3);
+            }
+        }
+        r[i] = v;
+    }
+}
+__device__ __forceinline__ void tc_store_kcontig(uint8_t* hi, uint8_t* lo, const float4 (&r)[2]) {
+    const int tid = threadIdx.x;
+    const int kc = tid & 3;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int row = (tid >> 2) + 64 * i;
+        float4 h, l;
+        split_tf32(r[i].x, h.x, l.x);
+        split_tf32(r[i].y, h.y, l.y);
+        split_tf32(r[i].z, h.z, l.z);
+        split_tf32(r[i].w, h.w, l.w);
+        const int off = kc * LBO_BYTES + row * 16;   // (row/8)*128 + (row%8)*16 == row*16
+        *reinterpret_cast<float4*>(hi + off) = h;
+        *reinterpret_cast<float4*>(lo + off) = l;
+    }
+}
+
+// row-contiguous storage ([k][row]): thread -> kc = tid/64, row pair rp = tid%64; four float2 loads
+// (k = 4 kc + i, rows 2 rp, 2 rp + 1) are transposed in registers into one float4 per row, so the
+// shared-memory stores stay 16-byte vectors along k.  r[0] = row 2rp, r[1] = row 2rp + 1.
+__device__ __forceinline__ void tc_load_rowcontig(const float* __restrict__ P, int64_t ld, int rows, int kend,
+                                                  int row0, int k0, int vec, const float* __restrict__ kscale,
+                                                  float4 (&r)[2]) {
+    const int tid = threadIdx.x;
+    const int row = row0 + (tid & 63) * 2;
+    const int kbase = k0 + (tid >> 6) * 4;
+    float a[4], b[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int k = kbase + i;
+        float x = 0.f, y = 0.f;
+        if (k < kend && row < rows) {
+            const float* src = P + (int64_t)k * ld + row;
+            if (vec && row + 1 < rows) {
+                const float2 t = __ldg(reinterpret_cast<const float2*>(src));
+                x = t.x; y = t.y;
+            } else {
+                x = __ldg(src);
+                if (row + 1 < rows) y = __ldg(src + 1);
+            }
+            if (kscale) {
+                const float s = __ldg(kscale + k);
+                x *= s; y *= s;
+            }
+        }
+        a[i] = x; b[i] = y;
+    }
+    r[0] = make_float4(a[0], a[1], a[2], a[3]);
+    r[1] = make_float4(b[0], b[1], b[2], b[3]);
+}
+__device__ __forceinline__ void tc_store_rowcontig(uint8_t* hi, uint8_t* lo, const float4 (&r)[2]) {
+    const int tid = threadIdx.x;
+    const int kc = tid >> 6;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int row = (tid & 63) * 2 + i;
+        float4 h, l;
+        split_tf32(r[i].x, h.x, l.x);
+        split_tf32(r[i].y, h.y, l.y);
+        split_tf32(r[i].z, h.z, l.z);
+        split_tf32(r[i].w, h.w, l.w);
+        const int off = kc * LBO_BYTES + row * 16;
+        *reinterpret_cast<float4*>(hi + off) = h;
+        *reinterpret_cast<float4*>(lo + off) = l;
+    }
+}
+
+template <bool TA, bool TB>
+__global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
+    extern __shared__ __align__(128) uint8_t dyn_smem[];
+    __shared__ __align__(8) uint64_t mma_bar[STAGES];
+    __shared__ uint32_t tmem_base_holder;
+
+    const int m0 = blockIdx.y * TM, n0 = blockIdx.x * TN;
+    if (p.lower && n0 > m0 + TM - 1) return;
+
+    int kb = 0, ke = p.K;
+    if (p.ktri) kb = (m0 / TK) * TK;
+    if (p.splitk > 1) {
+        const int ktiles = (ke - kb + TK - 1) / TK;
+        const int per = (ktiles + p.splitk - 1) / p.splitk;
+        const int b = kb + (int)blockIdx.z * per * TK;
+        ke = min(ke, b + per * TK);
+        kb = b;
+        if (kb >= ke) return;
+    }
+    const int num_k = (ke > kb) ? (ke - kb + TK - 1) / TK : 0;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dyn_smem) + 127) & ~(uintptr_t)127);
+
+    // ---- one-time setup: mbarriers + TMEM allocation ----
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) mbar_init(&mma_bar[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_holder)),
+                     "r"((uint32_t)TMEM_COLS)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_d = tmem_base_holder;
+
+    // MMA N: the valid columns of this tile rounded up to a legal UMMA N (multiple of 16)
+    const int n_valid = min(TN, p.N - n0);
+    const int n_mma = min(TN, ((n_valid + 15) / 16) * 16);
+    const uint32_t idesc = make_idesc(n_mma);
+
+    float4 ra[2], rb[2];
+    auto gload = [&](int k0) {
+        if (TA) tc_load_rowcontig(p.A, p.lda, p.M, ke, m0, k0, p.vecA, p.kscale, ra);
+        else    tc_load_kcontig(p.A, p.lda, p.M, ke, m0, k0, p.vecA, p.kscale, ra);
+        if (TB) tc_load_kcontig(p.B, p.ldb, p.N, ke, n0, k0, p.vecB, nullptr, rb);
+        else    tc_load_rowcontig(p.B, p.ldb, p.N, ke, n0, k0, p.vecB, nullptr, rb);
+    };
+    auto sstore = [&](int stage) {
+        uint8_t* base = smem + stage * STAGE_BYTES;
+        if (TA) tc_store_rowcontig(base, base + OPERAND_BYTES, ra);
+        else    tc_store_kcontig(base, base + OPERAND_BYTES, ra);
+        if (TB) tc_store_kcontig(base + 2 * OPERAND_BYTES, base + 3 * OPERAND_BYTES, rb);
+        else    tc_store_rowcontig(base + 2 * OPERAND_BYTES, base + 3 * OPERAND_BYTES, rb);
+    };
+
+    // epilogue constants
+    float alpha = p.alpha, r1c = p.r1coef;
+    if (p.alpha_dev) {
+        const float s = __ldg(p.alpha_dev);
+        alpha *= s;
+        r1c *= s;
+    }
+    const int q = warp & 3;                  // TMEM lane quadrant of this warp
+    const int m = m0 + q * 32 + lane;        // output row of this thread
+    const int col_half = (warp >> 2) * 64;   // warps 0-3: columns 0..63, warps 4-7: 64..127
+    const float um = (p.r1u && m < p.M) ? __ldg(p.r1u + m) * r1c : 0.f;
+
+    const int tiles_per_chunk = KCHUNK / TK;
+    const int num_chunks = num_k > 0 ? (num_k + tiles_per_chunk - 1) / tiles_per_chunk : 1;
+    if (num_k > 0) gload(kb);
+    for (int chunk = 0; chunk < num_chunks; ++chunk) {
+        const int kt_beg = chunk * tiles_per_chunk;
+        const int kt_end = min(num_k, kt_beg + tiles_per_chunk);
+        const bool first_chunk = (chunk == 0), last_chunk = (chunk == num_chunks - 1);
+        for (int kt = kt_beg; kt < kt_end; ++kt) {
+            const int stage = kt % STAGES;
+            if (kt >= STAGES) {
+                // the MMAs that read this stage (slab kt - STAGES) must have completed
+                mbar_wait(&mma_bar[stage], (uint32_t)((kt / STAGES - 1) & 1));
+            }
+            sstore(stage);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> tensor core
+            if (kt + 1 < num_k) gload(kb + (kt + 1) * TK);
+            __syncthreads();
+            if (tid == 0) {
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t sbase = smem_u32(smem + stage * STAGE_BYTES);
+#pragma unroll
+                for (int k8 = 0; k8 < TK / 8; ++k8) {
+                    const uint32_t koff = (uint32_t)(2 * k8 * LBO_BYTES);
+                    const uint64_t a_hi = make_desc(sbase + koff);
+                    const uint64_t a_lo = make_desc(sbase + OPERAND_BYTES + koff);
+                    const uint64_t b_hi = make_desc(sbase + 2 * OPERAND_BYTES + koff);
+                    const uint64_t b_lo = make_desc(sbase + 3 * OPERAND_BYTES + koff);
+                    const uint32_t acc = (kt > kt_beg || k8 > 0) ? 1u : 0u;
+                    mma_tf32(tmem_d + 128, a_lo, b_hi, idesc, acc);   // cross terms: own accumulator
+                    mma_tf32(tmem_d + 128, a_hi, b_lo, idesc, 1u);
+                    mma_tf32(tmem_d, a_hi, b_hi, idesc, acc);
+                }
+                mma_commit(&mma_bar[stage]);
+            }
+        }
+        if (kt_end > kt_beg) {
+            const int last = kt_end - 1;
+            mbar_wait(&mma_bar[last % STAGES], (uint32_t)((last / STAGES) & 1));
+        }
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+
+        // ------------- epilogue / flush: TMEM -> registers -> global -------------
+        // chunk 0 applies beta; later chunks accumulate onto C; bias / rank-1 / activation / mirror
+        // belong to the last chunk only.
+        const float beta = first_chunk ? p.beta : 1.f;
+#pragma unroll 1
+        for (int cc = 0; cc < 64; cc += 32) {
+            const int c0 = col_half + cc;
+            uint32_t v[32], w[32];
+            if (num_k > 0 && c0 < n_mma) {
+                const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)c0;
+                asm volatile(
+                    "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                    "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                    "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+                    : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                      "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                      "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                      "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                    : "r"(taddr)
+                    : "memory");
+                asm volatile(
+                    "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                    "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                    "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+                    : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]),
+                      "=r"(w[8]), "=r"(w[9]), "=r"(w[10]), "=r"(w[11]), "=r"(w[12]), "=r"(w[13]), "=r"(w[14]), "=r"(w[15]),
+                      "=r"(w[16]), "=r"(w[17]), "=r"(w[18]), "=r"(w[19]), "=r"(w[20]), "=r"(w[21]), "=r"(w[22]), "=r"(w[23]),
+                      "=r"(w[24]), "=r"(w[25]), "=r"(w[26]), "=r"(w[27]), "=r"(w[28]), "=r"(w[29]), "=r"(w[30]), "=r"(w[31])
+                    : "r"(taddr + 128u)
+                    : "memory");
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) { v[j] = 0u; w[j] = 0u; }
+            }
+            if (m >= p.M) continue;
+#pragma unroll
+            for (int j4 = 0; j4 < 32; j4 += 4) {
+                const int n = n0 + c0 + j4;
+                if (n >= p.N) continue;
+                float o[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) o[j] = alpha * (__uint_as_float(v[j4 + j]) + __uint_as_float(w[j4 + j]));
+                float* cp = p.C + (int64_t)m * p.ldc + n;
+                if (p.splitk > 1) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        if (n + j < p.N && (!p.lower || n + j <= m)) atomicAdd(cp + j, o[j]);
+                    continue;
+                }
+                const bool full = (n + 3 < p.N) && (!p.lower || n + 3 <= m);
+                if (beta != 0.f) {
+                    if (full && p.vecC) {
+                        const float4 c = *reinterpret_cast<const float4*>(cp);
+                        o[0] = fmaf(beta, c.x, o[0]); o[1] = fmaf(beta, c.y, o[1]);
+                        o[2] = fmaf(beta, c.z, o[2]); o[3] = fmaf(beta, c.w, o[3]);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            if (n + j < p.N && (!p.lower || n + j <= m)) o[j] = fmaf(beta, cp[j], o[j]);
+                    }
+                }
+                if (last_chunk) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        if (n + j < p.N) {
+                            if (p.bias) o[j] += __ldg(p.bias + n + j);
+                            if (p.r1u) o[j] = fmaf(um, __ldg(p.r1v + n + j), o[j]);
+                            if (p.act == 1) o[j] = tanhf(o[j]);
+                        }
+                    }
+                }
+                if (full && p.vecC) {
+                    *reinterpret_cast<float4*>(cp) = make_float4(o[0], o[1], o[2], o[3]);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        if (n + j < p.N && (!p.lower || n + j <= m)) cp[j] = o[j];
+                }
+                if (p.mirror && last_chunk) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        if (n + j < p.N && n + j < m) p.C[(int64_t)(n + j) * p.ldc + m] = o[j];
+                }
+            }
+        }
+        // all warps have drained the accumulators before the next chunk overwrites them
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    }
+
+    // ---- teardown: every warp is done reading TMEM (synchronised above) before warp 0 frees it ----
+    if (warp == 0) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)TMEM_COLS)
+                     : "memory");
+    }
+
+    // ---------------- Cholesky look-ahead (tile (0,0) only) ----------------
+    if (p.post_wdiag != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {
+        const int fail = factor_diag_block_regs(p.C, p.ldc, 0, p.post_nb, /*coherent=*/true,
+                                                reinterpret_cast<float*>(smem), p.post_wdiag, p.post_winv);
+        if (fail >= 0 && threadIdx.x == 0 && p.post_info) atomicCAS(p.post_info, 0, p.post_c0 + fail + 1);
+    }
+}
+
+}  // namespace
+
+int launch_gemm_tc(const KParams& p, bool transA, bool transB, dim3 grid, cudaStream_t stream) {
+    auto launch = [&](auto kern) -> int {
+        PB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, DYN_SMEM_BYTES));
+        kern<<<grid, NTHREADS, DYN_SMEM_BYTES, stream>>>(p);
+        return check_launch("gemm (tcgen05)");
+    };
+    if (!transA && !transB) return launch(tgemm_kernel<false, false>);
+    if (!transA && transB) return launch(tgemm_kernel<false, true>);
+    if (transA && !transB) return launch(tgemm_kernel<true, false>);
+    return launch(tgemm_kernel<true, true>);
+}
+
+}  // namespace pb

@@ -36,7 +36,7 @@ def test_loader_and_pure_host_entry_points():
     lib = _lib.load()
     assert lib.pinot_b200_abi_version() == 1
     assert _lib.potrf_workspace_bytes(0) == 0
-    assert _lib.potrf_workspace_bytes(65) == 2 * 64 * 64 * 4
+    assert _lib.potrf_workspace_bytes(65) == 2 * 2 * 64 * 64 * 4
     assert _lib.last_error() == "" or isinstance(_lib.last_error(), str)
 
 
