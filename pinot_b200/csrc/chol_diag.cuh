@@ -8,11 +8,11 @@
 // plain GEMM with M = L11^{-T}.
 //
 // Mapping: thread r (r < 128) keeps row r of the stacked matrix in 64 registers.  Step j:
-//   every thread scales its column-j entry by 1/sqrt(pivot) and publishes it (transposed) to shared
-//   memory; after one barrier each thread applies the rank-1 update to its remaining entries with
-//   63-j independent FMAs fed by broadcast LDS.128 reads.  Two barriers per step, no divergence,
-//   ~2000 FMAs per thread in total: a few microseconds instead of the tens a shared-memory
-//   read-modify-write formulation needs.
+//   every thread publishes its (unscaled) column-j entry to shared memory; after ONE barrier it
+//   reads the pivot and the column back (broadcast, 16-byte vector loads) and applies the scaled
+//   rank-1 update to its remaining entries with 63-j independent FMAs.  No divergence, ~2000 FMAs
+//   per thread in total: a few microseconds instead of the tens a shared-memory read-modify-write
+//   formulation needs.  Only warps 0-3 take part (named barrier 1), other warps return at once.
 #pragma once
 #include "common.cuh"
 
@@ -20,21 +20,20 @@ namespace pb {
 
 constexpr int DIAG_NB = 64;                 // panel width
 constexpr int DIAG_LT = DIAG_NB;            // Lt[j][c] = column j of the stacked factor, c < 64 (A rows only)
-constexpr int DIAG_SMEM_FLOATS = DIAG_NB * DIAG_LT + DIAG_NB;   // Lt + pivots
+constexpr int DIAG_SMEM_FLOATS = DIAG_NB * DIAG_LT;   // Lt (must be 16-byte aligned)
 
 // Factor the nb x nb block at (c0, c0) of `src` (lower triangle read) and write L11 (zero above the
 // diagonal) to wdiag and M = L11^{-T} (zero below it) to winv, both dense 64 x 64 (identity
 // padding beyond nb).  smem: DIAG_SMEM_FLOATS floats.  All threads of the CTA must call this
-// (blockDim.x >= 128); threads >= 128 only take part in the barriers.  `coherent` avoids the
+// (blockDim.x >= 128) after a CTA-wide barrier; threads >= 128 return immediately.  `coherent` avoids the
 // read-only path (the look-ahead epilogue reads values the same CTA has just written).
-// Returns the first failing pivot (0-based) or -1 (same value in every thread).
+// Returns the first failing pivot (0-based) or -1 (valid in threads < 128).
 __device__ __forceinline__ int factor_diag_block_regs(const float* src, int64_t ld, int c0, int nb, bool coherent,
                                                       float* smem, float* __restrict__ wdiag,
                                                       float* __restrict__ winv) {
     // NB `smem` must NOT be __restrict__: it carries data between threads across the barriers, and a
     // restrict-qualified pointer lets the compiler hoist those loads above __syncthreads().
     float* Lt = smem;                       // [64][64]: Lt[j][c] = L[c][j]
-    float* piv = smem + DIAG_NB * DIAG_LT;  // [64]
     const int tid = threadIdx.x;
     const bool active = tid < 2 * DIAG_NB;
     const bool is_a = tid < DIAG_NB;        // rows of A11; the rest are identity rows
@@ -68,24 +67,28 @@ __device__ __forceinline__ int factor_diag_block_regs(const float* src, int64_t 
         }
     }
     int fail = -1;
+    if (!active) return fail;   // NB the caller may only use the return value of thread 0
 #pragma unroll
     for (int j = 0; j < DIAG_NB; ++j) {
-        // pivot: thread j owns S[j][j]
-        if (tid == j) piv[j] = a[j];
-        __syncthreads();
-        float d = piv[j];
+        // publish the unscaled column j (entry j of it is the pivot S[j][j])
+        if (is_a) Lt[j * DIAG_LT + tid] = a[j];
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        float d = Lt[j * DIAG_LT + j];
         if (!(d > 0.f)) {   // also catches NaN
             if (fail < 0 && j < nb) fail = j;
             d = 1.f;
         }
-        const float inv = 1.f / sqrtf(d);
-        a[j] *= inv;                               // L[r][j] (thread j: sqrt(d)), or M[r][j]
-        if (is_a) Lt[j * DIAG_LT + tid] = a[j];    // publish column j of L (rows of A11 only)
-        __syncthreads();
-        if (active && j + 1 < DIAG_NB) {
-            const float x = a[j];
+        const float inv = rsqrtf(d);
+        const float y = a[j] * inv * inv;          // S[r][j] / d
+        a[j] *= inv;                               // L[r][j] (row j: sqrt(d)), or M[r][j]
+        // S[r][c] -= S[r][j] S[c][j] / d for c > j; column read in aligned 16-byte pieces
 #pragma unroll
-            for (int c = j + 1; c < DIAG_NB; ++c) a[c] = fmaf(-x, Lt[j * DIAG_LT + c], a[c]);
+        for (int c4 = ((j + 1) / 4) * 4; c4 < DIAG_NB; c4 += 4) {
+            const float4 l = *reinterpret_cast<const float4*>(Lt + j * DIAG_LT + c4);
+            if (c4 + 0 > j) a[c4 + 0] = fmaf(-y, l.x, a[c4 + 0]);
+            if (c4 + 1 > j) a[c4 + 1] = fmaf(-y, l.y, a[c4 + 1]);
+            if (c4 + 2 > j) a[c4 + 2] = fmaf(-y, l.z, a[c4 + 2]);
+            if (c4 + 3 > j) a[c4 + 3] = fmaf(-y, l.w, a[c4 + 3]);
         }
     }
     // results: thread r < 64 holds row r of L11 (entries c <= r), thread 64 + r row r of M (c >= r)

@@ -17,7 +17,8 @@
 //     terms get their own accumulator (TMEM columns 128-255) and both are flushed into C every 512
 //     K-columns, which bounds the accumulation error independently of K;
 //   * the epilogue reads the accumulator back with tcgen05.ld (each warp its 32 TMEM lanes, i.e. 32
-//     rows; warps 0-3 the left 64 columns, warps 4-7 the right ones) and applies the same fused
+//     rows; warps 0-3 the left 64 columns, warps 4-7 the right ones), transposes 32x32 blocks through
+//     shared memory so that C is read and written in row-contiguous 128-byte pieces, and applies the same fused
 //     epilogue as the FFMA kernel (alpha/beta, bias, tanh, rank-1 term, lower/mirror masks,
 //     split-K atomics, Cholesky look-ahead).
 #include "gemm_params.cuh"
@@ -38,6 +39,7 @@ constexpr int STAGE_BYTES = 4 * OPERAND_BYTES;
 constexpr int PIPE_BYTES = STAGES * STAGE_BYTES;
 constexpr int DIAG_BYTES = DIAG_SMEM_FLOATS * 4;
 constexpr int DYN_SMEM_BYTES = (PIPE_BYTES > DIAG_BYTES ? PIPE_BYTES : DIAG_BYTES) + 128;
+constexpr int EPI_LD = 36;                     // floats per row of a warp's 32x32 epilogue staging tile
 constexpr int TMEM_COLS = 256;                // [0,128): hi.hi accumulator, [128,256): cross terms
 constexpr int KCHUNK = 512;                   // accumulator is flushed to C every KCHUNK columns
 
@@ -267,9 +269,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
         r1c *= s;
     }
     const int q = warp & 3;                  // TMEM lane quadrant of this warp
-    const int m = m0 + q * 32 + lane;        // output row of this thread
     const int col_half = (warp >> 2) * 64;   // warps 0-3: columns 0..63, warps 4-7: 64..127
-    const float um = (p.r1u && m < p.M) ? __ldg(p.r1u + m) * r1c : 0.f;
 
     const int tiles_per_chunk = KCHUNK / TK;
     const int num_chunks = num_k > 0 ? (num_k + tiles_per_chunk - 1) / tiles_per_chunk : 1;
@@ -347,14 +347,28 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
 #pragma unroll
                 for (int j = 0; j < 32; ++j) { v[j] = 0u; w[j] = 0u; }
             }
-            if (m >= p.M) continue;
+            // transpose through shared memory (the pipeline stages are idle now) so that global
+            // accesses are row-contiguous: 8 lanes x 16 B cover one row's 32 columns, 4 rows per access
+            float* tile = reinterpret_cast<float*>(smem) + warp * (32 * EPI_LD);
 #pragma unroll
-            for (int j4 = 0; j4 < 32; j4 += 4) {
-                const int n = n0 + c0 + j4;
-                if (n >= p.N) continue;
-                float o[4];
-#pragma unroll
-                for (int j = 0; j < 4; ++j) o[j] = alpha * (__uint_as_float(v[j4 + j]) + __uint_as_float(w[j4 + j]));
+            for (int i = 0; i < 8; ++i) {
+                float4 t;
+                t.x = __uint_as_float(v[4 * i + 0]) + __uint_as_float(w[4 * i + 0]);
+                t.y = __uint_as_float(v[4 * i + 1]) + __uint_as_float(w[4 * i + 1]);
+                t.z = __uint_as_float(v[4 * i + 2]) + __uint_as_float(w[4 * i + 2]);
+                t.w = __uint_as_float(v[4 * i + 3]) + __uint_as_float(w[4 * i + 3]);
+                *reinterpret_cast<float4*>(tile + lane * EPI_LD + 4 * i) = t;
+            }
+            __syncwarp();
+#pragma unroll 2
+            for (int t8 = 0; t8 < 8; ++t8) {
+                const int rl = t8 * 4 + (lane >> 3);
+                const int c4 = (lane & 7) * 4;
+                const int m = m0 + q * 32 + rl;
+                const int n = n0 + c0 + c4;
+                if (m >= p.M || n >= p.N) continue;
+                const float4 acc = *reinterpret_cast<const float4*>(tile + rl * EPI_LD + c4);
+                float o[4] = {alpha * acc.x, alpha * acc.y, alpha * acc.z, alpha * acc.w};
                 float* cp = p.C + (int64_t)m * p.ldc + n;
                 if (p.splitk > 1) {
 #pragma unroll
@@ -375,6 +389,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
                     }
                 }
                 if (last_chunk) {
+                    const float um = p.r1u ? __ldg(p.r1u + m) * r1c : 0.f;
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
                         if (n + j < p.N) {
@@ -397,6 +412,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
                         if (n + j < p.N && n + j < m) p.C[(int64_t)(n + j) * p.ldc + m] = o[j];
                 }
             }
+            __syncwarp();
         }
         // all warps have drained the accumulators before the next chunk overwrites them
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
