@@ -69,26 +69,22 @@ class GradientBucket:
     def allreduce(self, average=False):
         if world_size() == 1:
             return
-        off = 0
+        grads = []
         for p in self.params:
-            n = p.numel()
             if p.grad is None:
-                self.flat[off:off + n].zero_()
-            else:
-                self.flat[off:off + n].copy_(p.grad.reshape(-1))
-            off += n
+                p.grad = torch.zeros_like(p)
+            grads.append(p.grad)
+        # one gather kernel, one collective, one scatter kernel
+        torch.cat([g.reshape(-1) for g in grads], out=self.flat)
         dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
         if average:
             self.flat.div_(world_size())
-        off = 0
+        views, off = [], 0
         for p in self.params:
             n = p.numel()
-            g = self.flat[off:off + n].view_as(p)
-            if p.grad is None:
-                p.grad = g.clone()
-            else:
-                p.grad.copy_(g)
+            views.append(self.flat[off:off + n].view_as(p))
             off += n
+        torch._foreach_copy_(grads, views)
 
 
 def broadcast_parameters(module, src=0):
