@@ -8,16 +8,107 @@
 // neighbour rows belong to the same molecule and are served from L1/L2.
 #include "common.cuh"
 #include "../../include/pinot_b200.h"
+#include <stdlib.h>
 
 namespace {
 
 // out[i, :] = dst_scale[i] * sum_{e in [indptr[i], indptr[i+1])} src_scale[idx[e]] * x[idx[e], :]
-template <int VEC>
-__global__ void __launch_bounds__(256)
+//
+// Each thread owns one 16-byte (VEC = 4) column slice of ITEMS destination rows that are
+// `row_stride` apart, and walks their edge lists in lock-step: the ITEMS row-pointer loads, then
+// the ITEMS index loads, then the ITEMS neighbour-row gathers of one edge slot are all issued
+// before any of them is consumed.  The three dependent load levels (pointer -> index -> row) are
+// what limits a one-row-per-thread version to about half of the HBM rate; ITEMS independent chains
+// per thread keep enough bytes in flight.
+
+// FV = float4 slices per row when known at compile time (32 for H = 128, 16 for H = 64, 8 for H = 32),
+// 0 = run-time `feat_v`.  Offsets are 32-bit (in units of one slice): the host falls back to the wide
+// kernel when n_rows * feat_v does not fit.
+template <int VEC, int FV, int MP_ITEMS, int MINB>
+__global__ void __launch_bounds__(256, MINB)
 mp_aggregate_kernel(const float* __restrict__ x, float* __restrict__ out,
                     const int32_t* __restrict__ indptr, const int32_t* __restrict__ indices,
                     const float* __restrict__ src_scale, const float* __restrict__ dst_scale,
-                    int64_t n_dst, int feat_v) {
+                    int n_dst, int feat_v_rt) {
+    const int feat_v = FV > 0 ? FV : feat_v_rt;
+    const int rows_per_block = 256 / feat_v;             // feat_v <= 256 on this path
+    const int lrow = threadIdx.x / feat_v;
+    const int c = threadIdx.x - lrow * feat_v;
+    if (lrow >= rows_per_block) return;
+    const int row0 = (int)blockIdx.x * MP_ITEMS * rows_per_block + lrow;
+
+    int beg[MP_ITEMS], deg[MP_ITEMS];
+    float acc[MP_ITEMS][VEC];
+#pragma unroll
+    for (int i = 0; i < MP_ITEMS; ++i) {
+        const int row = row0 + i * rows_per_block;
+        beg[i] = 0;
+        deg[i] = 0;
+        if (row < n_dst) {
+            const int2 pq = make_int2(__ldg(indptr + row), __ldg(indptr + row + 1));
+            beg[i] = pq.x;
+            deg[i] = pq.y - pq.x;
+        }
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) acc[i][v] = 0.f;
+    }
+    int maxdeg = 0;
+#pragma unroll
+    for (int i = 0; i < MP_ITEMS; ++i) maxdeg = max(maxdeg, deg[i]);
+
+    for (int e = 0; e < maxdeg; ++e) {
+        int j[MP_ITEMS];
+        float s[MP_ITEMS];
+#pragma unroll
+        for (int i = 0; i < MP_ITEMS; ++i) j[i] = (e < deg[i]) ? __ldg(indices + beg[i] + e) : -1;
+        if (src_scale) {
+#pragma unroll
+            for (int i = 0; i < MP_ITEMS; ++i) s[i] = (j[i] >= 0) ? __ldg(src_scale + j[i]) : 0.f;
+        } else {
+#pragma unroll
+            for (int i = 0; i < MP_ITEMS; ++i) s[i] = (j[i] >= 0) ? 1.f : 0.f;
+        }
+        if (VEC == 4) {
+            const float4* x4 = reinterpret_cast<const float4*>(x);
+            float4 v[MP_ITEMS];
+#pragma unroll
+            for (int i = 0; i < MP_ITEMS; ++i) v[i] = __ldg(x4 + (unsigned)(max(j[i], 0) * feat_v + c));
+#pragma unroll
+            for (int i = 0; i < MP_ITEMS; ++i) {
+                acc[i][0] = fmaf(s[i], v[i].x, acc[i][0]);
+                acc[i][1 % VEC] = fmaf(s[i], v[i].y, acc[i][1 % VEC]);
+                acc[i][2 % VEC] = fmaf(s[i], v[i].z, acc[i][2 % VEC]);
+                acc[i][3 % VEC] = fmaf(s[i], v[i].w, acc[i][3 % VEC]);
+            }
+        } else {
+            float v[MP_ITEMS];
+#pragma unroll
+            for (int i = 0; i < MP_ITEMS; ++i) v[i] = __ldg(x + (unsigned)(max(j[i], 0) * feat_v + c));
+#pragma unroll
+            for (int i = 0; i < MP_ITEMS; ++i) acc[i][0] = fmaf(s[i], v[i], acc[i][0]);
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < MP_ITEMS; ++i) {
+        const int row = row0 + i * rows_per_block;
+        if (row >= n_dst) continue;
+        const float d = dst_scale ? __ldg(dst_scale + row) : 1.f;
+        if (VEC == 4) {
+            reinterpret_cast<float4*>(out)[(unsigned)(row * feat_v + c)] =
+                make_float4(acc[i][0] * d, acc[i][1 % VEC] * d, acc[i][2 % VEC] * d, acc[i][3 % VEC] * d);
+        } else {
+            out[(unsigned)(row * feat_v + c)] = acc[i][0] * d;
+        }
+    }
+}
+
+// Wide rows (more than 256 column slices per row): one thread per (row, slice), plain loop.
+template <int VEC>
+__global__ void __launch_bounds__(256)
+mp_aggregate_wide_kernel(const float* __restrict__ x, float* __restrict__ out,
+                         const int32_t* __restrict__ indptr, const int32_t* __restrict__ indices,
+                         const float* __restrict__ src_scale, const float* __restrict__ dst_scale,
+                         int64_t n_dst, int feat_v) {
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t row = t / feat_v;
     if (row >= n_dst) return;
@@ -26,36 +117,7 @@ mp_aggregate_kernel(const float* __restrict__ x, float* __restrict__ out,
     float acc[VEC];
 #pragma unroll
     for (int v = 0; v < VEC; ++v) acc[v] = 0.f;
-
-    int e = beg;
-    // 4 neighbours in flight per thread: index loads first, then the row gathers.
-    for (; e + 4 <= end; e += 4) {
-        int j[4];
-        float s[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) j[u] = __ldg(indices + e + u);
-#pragma unroll
-        for (int u = 0; u < 4; ++u) s[u] = src_scale ? __ldg(src_scale + j[u]) : 1.f;
-        if (VEC == 4) {
-            float4 v[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u) v[u] = pb::ldg4(x + ((int64_t)j[u] * feat_v + c) * 4);
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                acc[0] = fmaf(s[u], v[u].x, acc[0]);
-                acc[1 % VEC] = fmaf(s[u], v[u].y, acc[1 % VEC]);
-                acc[2 % VEC] = fmaf(s[u], v[u].z, acc[2 % VEC]);
-                acc[3 % VEC] = fmaf(s[u], v[u].w, acc[3 % VEC]);
-            }
-        } else {
-            float v[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u) v[u] = __ldg(x + (int64_t)j[u] * feat_v + c);
-#pragma unroll
-            for (int u = 0; u < 4; ++u) acc[0] = fmaf(s[u], v[u], acc[0]);
-        }
-    }
-    for (; e < end; ++e) {
+    for (int e = beg; e < end; ++e) {
         const int j = __ldg(indices + e);
         const float s = src_scale ? __ldg(src_scale + j) : 1.f;
         if (VEC == 4) {
@@ -70,8 +132,8 @@ mp_aggregate_kernel(const float* __restrict__ x, float* __restrict__ out,
     }
     const float d = dst_scale ? __ldg(dst_scale + row) : 1.f;
     if (VEC == 4) {
-        float4 o = make_float4(acc[0] * d, acc[1 % VEC] * d, acc[2 % VEC] * d, acc[3 % VEC] * d);
-        *reinterpret_cast<float4*>(out + (row * feat_v + c) * 4) = o;
+        *reinterpret_cast<float4*>(out + (row * feat_v + c) * 4) =
+            make_float4(acc[0] * d, acc[1 % VEC] * d, acc[2 % VEC] * d, acc[3 % VEC] * d);
     } else {
         out[row * feat_v + c] = acc[0] * d;
     }
@@ -157,15 +219,36 @@ int launch_aggregate(const float* x, float* out, const int32_t* indptr, const in
     if (n_dst == 0) return pb::PB_OK;
     PB_REQUIRE(x && out && indptr, "%s: null pointer", who);
     PB_REQUIRE(x != out, "%s: in-place aggregation is not supported", who);
-    if (can_vec4(feat, x, out)) {
-        const int fv = (int)(feat / 4);
-        const int64_t threads = n_dst * fv;
-        mp_aggregate_kernel<4><<<(unsigned)pb::ceil_div(threads, 256), 256, 0, stream>>>(
-            x, out, indptr, indices, src_scale, dst_scale, n_dst, fv);
+    const bool vec = can_vec4(feat, x, out);
+    const int64_t fv = vec ? feat / 4 : feat;
+    // the row-batched kernel indexes with 32-bit slice offsets; padded rows (j = -1 -> row 0) read row 0
+    const bool fits32 = fv <= 256 && n_dst * fv < (1ll << 31);
+    if (fits32) {
+        static const int variant = [] { const char* v = getenv("PINOT_B200_MP_VARIANT"); return v ? atoi(v) : 0; }();
+        const int rows_per_block = 256 / (int)fv;
+#define PB_LAUNCH_MP(V, F, I, B)                                                                              \
+        mp_aggregate_kernel<V, F, I, B><<<(unsigned)pb::ceil_div(n_dst, (int64_t)rows_per_block * I), 256, 0, stream>>>( \
+            x, out, indptr, indices, src_scale, dst_scale, (int)n_dst, (int)fv)
+#define PB_LAUNCH_MP_V(I, B)                                   \
+        do {                                                   \
+            if (vec && fv == 32) PB_LAUNCH_MP(4, 32, I, B);    \
+            else if (vec && fv == 16) PB_LAUNCH_MP(4, 16, I, B); \
+            else if (vec && fv == 8) PB_LAUNCH_MP(4, 8, I, B); \
+            else if (vec) PB_LAUNCH_MP(4, 0, I, B);            \
+            else PB_LAUNCH_MP(1, 0, I, B);                     \
+        } while (0)
+        if (variant == 1) PB_LAUNCH_MP_V(2, 8);
+        else if (variant == 2) PB_LAUNCH_MP_V(2, 6);
+        else if (variant == 3) PB_LAUNCH_MP_V(1, 8);
+        else PB_LAUNCH_MP_V(4, 5);
+#undef PB_LAUNCH_MP_V
+#undef PB_LAUNCH_MP
+    } else if (vec) {
+        mp_aggregate_wide_kernel<4><<<(unsigned)pb::ceil_div(n_dst * fv, 256), 256, 0, stream>>>(
+            x, out, indptr, indices, src_scale, dst_scale, n_dst, (int)fv);
     } else {
-        const int64_t threads = n_dst * feat;
-        mp_aggregate_kernel<1><<<(unsigned)pb::ceil_div(threads, 256), 256, 0, stream>>>(
-            x, out, indptr, indices, src_scale, dst_scale, n_dst, (int)feat);
+        mp_aggregate_wide_kernel<1><<<(unsigned)pb::ceil_div(n_dst * fv, 256), 256, 0, stream>>>(
+            x, out, indptr, indices, src_scale, dst_scale, n_dst, (int)fv);
     }
     return pb::check_launch(who);
 }
