@@ -280,6 +280,18 @@ chol_diag_kernel(const float* __restrict__ E, int64_t ld, int c0, int nb, float*
     if (fail >= 0 && threadIdx.x == 0) atomicCAS(info, 0, c0 + fail + 1);
 }
 
+// Outer block width of the two-level sweep (multiple of NB).  PINOT_B200_OUTER_BLOCK overrides.
+int64_t outer_block_width(int64_t n) {
+    static const int64_t forced = [] {
+        const char* v = getenv("PINOT_B200_OUTER_BLOCK");
+        const int64_t w = v ? atoll(v) : 0;
+        return (w >= NB && w % NB == 0) ? w : (int64_t)0;
+    }();
+    if (forced) return forced;
+    if (n >= 6144) return 512;
+    return NB;
+}
+
 bool lookahead_enabled() {
     static const bool on = [] {
         const char* v = getenv("PINOT_B200_LOOKAHEAD");
@@ -323,45 +335,68 @@ int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, i
     float* winv = wdiag + nblk * NB * NB;
     const int64_t r_total = n_ext_dense + (ext_identity ? n : 0);
     const bool lookahead = lookahead_enabled();
-    // Per column block [c0, c1):
-    //   (a) the diagonal block's factor L11 and M = L11^{-T} are in the workspace (first block: a
-    //       one-CTA kernel; later blocks: produced by tile (0,0) of the previous trailing update
-    //       while the other tiles are still being computed);
-    //   (b) panel "TRSM" as a GEMM: rows below the block and the active extension rows *= M;
-    //   (c) rank-nb trailing update of everything to the right (lower triangle + extension rows).
-    for (int64_t c0 = 0; c0 < n; c0 += NB) {
-        const int nb = (int)((n - c0) < NB ? (n - c0) : NB);
-        const int64_t c1 = c0 + nb, b = c0 / NB;
-        const int64_t r_act = ext_identity ? (n_ext_dense + c1) : r_total;
-        const int64_t row_end = n + r_act;
-        if (c0 == 0 || !lookahead) {
-            chol_diag_kernel<<<1, 256, 0, stream>>>(e, ld, (int)c0, nb, wdiag + b * NB * NB, winv + b * NB * NB, info);
-            int rc = pb::check_launch("chol_diag");
-            if (rc) return rc;
-        }
-        if (row_end > c1) {
-            pb::GemmParams g;   // in place: every CTA owns whole rows of the panel (N = nb <= one tile)
-            g.M = (int)(row_end - c1); g.N = nb; g.K = nb;
-            g.A = e + c1 * ld + c0; g.lda = ld;
-            g.B = winv + b * NB * NB; g.ldb = NB;
-            g.C = e + c1 * ld + c0; g.ldc = ld;
-            int rc = pb::gemm(g, stream);
-            if (rc) return rc;
-        }
-        if (c1 < n) {
-            pb::GemmParams g;
-            g.M = (int)(row_end - c1); g.N = (int)(n - c1); g.K = nb;
-            g.A = e + c1 * ld + c0; g.lda = ld; g.transA = false;
-            g.B = e + c1 * ld + c0; g.ldb = ld; g.transB = true;
-            g.C = e + c1 * ld + c1; g.ldc = ld;
-            g.alpha = -1.f; g.beta = 1.f; g.lower = 1;
-            if (lookahead) {
-                g.post_wdiag = wdiag + (b + 1) * NB * NB;
-                g.post_winv = winv + (b + 1) * NB * NB;
-                g.post_info = info;
-                g.post_nb = (int)((n - c1) < NB ? (n - c1) : NB);
-                g.post_c0 = (int)c1;
+    // Two-level blocking.  Column blocks of width NB are grouped into outer blocks of width W; the
+    // rank-NB updates inside an outer block only touch that block's remaining columns, and
+    // everything to the right of it receives ONE rank-W update per outer block.  The trailing
+    // matrix is then read and written n/W times instead of n/NB times, which is what bounds large
+    // factorisations (n = 16384: 275 GB of HBM traffic with W = NB = 64); small ones are bound by
+    // the length of the dependent launch chain and keep W = NB.
+    const int64_t W = outer_block_width(n);
+    auto active_rows_end = [&](int64_t c1) { return n + (ext_identity ? (n_ext_dense + c1) : r_total); };
+    auto attach_lookahead = [&](pb::GemmParams& g, int64_t c1) {
+        if (!lookahead) return;
+        const int64_t b1 = c1 / NB;
+        g.post_wdiag = wdiag + b1 * NB * NB;
+        g.post_winv = winv + b1 * NB * NB;
+        g.post_info = info;
+        g.post_nb = (int)((n - c1) < NB ? (n - c1) : NB);
+        g.post_c0 = (int)c1;
+    };
+    for (int64_t J0 = 0; J0 < n; J0 += W) {
+        const int64_t J1 = (J0 + W < n) ? J0 + W : n;
+        for (int64_t c0 = J0; c0 < J1; c0 += NB) {
+            const int nb = (int)((n - c0) < NB ? (n - c0) : NB);
+            const int64_t c1 = c0 + nb, b = c0 / NB;
+            const int64_t row_end = active_rows_end(c1);
+            // (a) factor of the diagonal block: first block, or no look-ahead
+            if (c0 == 0 || !lookahead) {
+                chol_diag_kernel<<<1, 256, 0, stream>>>(e, ld, (int)c0, nb, wdiag + b * NB * NB, winv + b * NB * NB, info);
+                int rc = pb::check_launch("chol_diag");
+                if (rc) return rc;
             }
+            // (b) panel "TRSM" as a GEMM with M = L11^{-T}, in place (each CTA owns whole rows)
+            if (row_end > c1) {
+                pb::GemmParams g;
+                g.M = (int)(row_end - c1); g.N = nb; g.K = nb;
+                g.A = e + c1 * ld + c0; g.lda = ld;
+                g.B = winv + b * NB * NB; g.ldb = NB;
+                g.C = e + c1 * ld + c0; g.ldc = ld;
+                int rc = pb::gemm(g, stream);
+                if (rc) return rc;
+            }
+            // (c) rank-nb update of the rest of this outer block (lower triangle + extension rows)
+            if (c1 < J1) {
+                pb::GemmParams g;
+                g.M = (int)(row_end - c1); g.N = (int)(J1 - c1); g.K = nb;
+                g.A = e + c1 * ld + c0; g.lda = ld; g.transA = false;
+                g.B = e + c1 * ld + c0; g.ldb = ld; g.transB = true;
+                g.C = e + c1 * ld + c1; g.ldc = ld;
+                g.alpha = -1.f; g.beta = 1.f; g.lower = 1;
+                attach_lookahead(g, c1);
+                int rc = pb::gemm(g, stream);
+                if (rc) return rc;
+            }
+        }
+        // (d) rank-(J1 - J0) update of everything to the right of the outer block
+        if (J1 < n) {
+            const int64_t row_end = active_rows_end(J1);
+            pb::GemmParams g;
+            g.M = (int)(row_end - J1); g.N = (int)(n - J1); g.K = (int)(J1 - J0);
+            g.A = e + J1 * ld + J0; g.lda = ld; g.transA = false;
+            g.B = e + J1 * ld + J0; g.ldb = ld; g.transB = true;
+            g.C = e + J1 * ld + J1; g.ldc = ld;
+            g.alpha = -1.f; g.beta = 1.f; g.lower = 1;
+            attach_lookahead(g, J1);
             int rc = pb::gemm(g, stream);
             if (rc) return rc;
         }
