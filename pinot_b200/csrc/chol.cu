@@ -319,8 +319,10 @@ extern "C" {
 
 int64_t pinot_b200_potrf_workspace_bytes(int64_t n) {
     if (n < 0) return -1;
-    // per column block: L11 (deferred diagonal write-back) and L11^{-T} (panel TRSM as a GEMM)
-    return (int64_t)sizeof(float) * pb::ceil_div(n, NB) * NB * NB * 2;
+    // per column block: L11 (deferred diagonal write-back), L11^{-T} (panel TRSM as a GEMM) and a
+    // "factor published" flag for the fused panel solve
+    const int64_t nblk = pb::ceil_div(n, NB);
+    return (int64_t)sizeof(float) * nblk * NB * NB * 2 + pb::ceil_div(nblk * (int64_t)sizeof(int), 256) * 256;
 }
 
 int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, int ext_identity,
@@ -333,8 +335,14 @@ int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, i
     const int64_t nblk = pb::ceil_div(n, NB);
     float* wdiag = static_cast<float*>(workspace);
     float* winv = wdiag + nblk * NB * NB;
+    int* flags = reinterpret_cast<int*>(winv + nblk * NB * NB);
+    PB_CUDA(cudaMemsetAsync(flags, 0, sizeof(int) * nblk, stream));
     const int64_t r_total = n_ext_dense + (ext_identity ? n : 0);
-    const bool lookahead = lookahead_enabled();
+    // the fused look-ahead kernel is built for 16-byte aligned rows only (ld % 4 == 0)
+    const bool lookahead = lookahead_enabled() && (ld % 4 == 0) && pb::aligned16(e);
+    // With the tensor-core GEMM the panel solve of block b+1 is fused into the update that also
+    // factors its diagonal block (one launch per sweep step instead of two).
+    const bool fused = lookahead && pb::gemm_uses_tensor_cores();
     // Two-level blocking.  Column blocks of width NB are grouped into outer blocks of width W; the
     // rank-NB updates inside an outer block only touch that block's remaining columns, and
     // everything to the right of it receives ONE rank-W update per outer block.  The trailing
@@ -351,6 +359,13 @@ int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, i
         g.post_info = info;
         g.post_nb = (int)((n - c1) < NB ? (n - c1) : NB);
         g.post_c0 = (int)c1;
+        if (fused) {
+            g.post_flag = flags + b1;
+            g.post_solve = 1;
+            // the identity rows that enter with block b1 ride along (their update is a no-op) so
+            // that tile column 0 solves them too
+            g.M = (int)(active_rows_end(c1 + g.post_nb) - c1);
+        }
     };
     for (int64_t J0 = 0; J0 < n; J0 += W) {
         const int64_t J1 = (J0 + W < n) ? J0 + W : n;
@@ -364,8 +379,9 @@ int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, i
                 int rc = pb::check_launch("chol_diag");
                 if (rc) return rc;
             }
-            // (b) panel "TRSM" as a GEMM with M = L11^{-T}, in place (each CTA owns whole rows)
-            if (row_end > c1) {
+            // (b) panel "TRSM" as a GEMM with M = L11^{-T}, in place (each CTA owns whole rows); in the
+            //     fused scheme only the very first panel needs it
+            if (row_end > c1 && (c0 == 0 || !fused)) {
                 pb::GemmParams g;
                 g.M = (int)(row_end - c1); g.N = nb; g.K = nb;
                 g.A = e + c1 * ld + c0; g.lda = ld;

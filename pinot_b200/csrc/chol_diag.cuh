@@ -15,6 +15,9 @@
 //   formulation needs.  Only warps 0-3 take part (named barrier 1), other warps return at once.
 #pragma once
 #include "common.cuh"
+#ifndef PB_STAMP
+#define PB_STAMP(i)
+#endif
 
 namespace pb {
 
@@ -105,6 +108,129 @@ __device__ __forceinline__ int factor_diag_block_regs(const float* src, int64_t 
         }
     }
     return fail;
+}
+
+// ---- fused panel solve ------------------------------------------------------------------------
+constexpr int SOLVE_LD = DIAG_NB + 1;                                       // padded row of the staged X tile
+constexpr int SOLVE_SMEM_FLOATS = 128 * SOLVE_LD + 12 + DIAG_NB * DIAG_NB;  // X tile (128 x 64) + M (64 x 64)
+
+__device__ __forceinline__ void publish_flag(int* flag) {
+    __threadfence();          // this thread's stores (L11 / M) are visible device-wide ...
+    __syncthreads();
+    if (threadIdx.x == 0) atomicExch(flag, 1);   // ... before the flag is
+}
+__device__ __forceinline__ void wait_flag(const int* flag) {
+    if (threadIdx.x == 0) {
+        int v;
+        do {
+            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+            if (v == 0) __nanosleep(64);
+        } while (v == 0);
+    }
+    __syncthreads();
+}
+
+// C[m][0:nb] <- C[m][0:nb] * M  for the rows m in [m0, m0 + 128) of C with nb <= m < rows,
+// M = winv (64 x 64, upper triangular, dense).  256 threads; smem: SOLVE_SMEM_FLOATS floats.
+// The rows were written by this CTA earlier in the same kernel: they are re-read through L2.
+__device__ __forceinline__ void panel_solve_tile(float* C, int64_t ldc, int m0, int rows, int nb,
+                                                 const float* winv, float* smem) {
+    float* Xs = smem;                            // [128][SOLVE_LD]
+    float* Ms = smem + 128 * SOLVE_LD + 12;      // [64][64], 16-byte aligned (128 * 65 + 12 = 8332 floats)
+    const int tid = threadIdx.x;
+    const bool vec = ((ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(C) & 15u) == 0);
+    {
+        // all loads first (they are independent), then the shared-memory stores: one L2 round trip
+        float4 mreg[4], xreg[8];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) mreg[i] = __ldcg(reinterpret_cast<const float4*>(winv) + tid + i * 256);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int idx = tid + i * 256;          // float4 index in the 128 x 16 tile
+            const int r = idx >> 4, c = (idx & 15) * 4;
+            const int m = m0 + r;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (m >= nb && m < rows && c < nb) {
+                const float* src = C + (int64_t)m * ldc + c;
+                if (vec && c + 3 < nb) {
+                    v = __ldcg(reinterpret_cast<const float4*>(src));
+                } else {
+                    v.x = __ldcg(src);
+                    if (c + 1 < nb) v.y = __ldcg(src + 1);
+                    if (c + 2 < nb) v.z = __ldcg(src + 2);
+                    if (c + 3 < nb) v.w = __ldcg(src + 3);
+                }
+            }
+            xreg[i] = v;
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) reinterpret_cast<float4*>(Ms)[tid + i * 256] = mreg[i];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int idx = tid + i * 256;
+            const int r = idx >> 4, c = (idx & 15) * 4;
+            Xs[r * SOLVE_LD + c + 0] = xreg[i].x;
+            Xs[r * SOLVE_LD + c + 1] = xreg[i].y;
+            Xs[r * SOLVE_LD + c + 2] = xreg[i].z;
+            Xs[r * SOLVE_LD + c + 3] = xreg[i].w;
+        }
+    }
+    __syncthreads();
+    PB_STAMP(8);
+    // warp w: column group (w & 3) of 16 columns, row block (w >> 2) of 64 rows; lane l handles rows
+    // l and l + 32 of that block.  Every lane of a warp reads the same M addresses (broadcast) and
+    // its own conflict-free X rows: 2 scalar + 4 vector LDS per 32 FMAs.
+    const int warp = tid >> 5, lane = tid & 31;
+    const int cg = (warp & 3) * 16;
+    const int r0 = (warp >> 2) * 64 + lane, r1 = r0 + 32;
+    float acc0[16], acc1[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) { acc0[j] = 0.f; acc1[j] = 0.f; }
+#pragma unroll 4
+    for (int k = 0; k < DIAG_NB; ++k) {
+        const float x0 = Xs[r0 * SOLVE_LD + k];
+        const float x1 = Xs[r1 * SOLVE_LD + k];
+#pragma unroll
+        for (int j4 = 0; j4 < 16; j4 += 4) {
+            const float4 mv = *reinterpret_cast<const float4*>(Ms + k * DIAG_NB + cg + j4);
+            acc0[j4 + 0] = fmaf(x0, mv.x, acc0[j4 + 0]);
+            acc0[j4 + 1] = fmaf(x0, mv.y, acc0[j4 + 1]);
+            acc0[j4 + 2] = fmaf(x0, mv.z, acc0[j4 + 2]);
+            acc0[j4 + 3] = fmaf(x0, mv.w, acc0[j4 + 3]);
+            acc1[j4 + 0] = fmaf(x1, mv.x, acc1[j4 + 0]);
+            acc1[j4 + 1] = fmaf(x1, mv.y, acc1[j4 + 1]);
+            acc1[j4 + 2] = fmaf(x1, mv.z, acc1[j4 + 2]);
+            acc1[j4 + 3] = fmaf(x1, mv.w, acc1[j4 + 3]);
+        }
+    }
+    __syncthreads();
+    PB_STAMP(9);
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        Xs[r0 * SOLVE_LD + cg + j] = acc0[j];
+        Xs[r1 * SOLVE_LD + cg + j] = acc1[j];
+    }
+    __syncthreads();
+    PB_STAMP(10);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int idx = tid + i * 256;
+        const int rr = idx >> 4, c = (idx & 15) * 4;
+        const int m = m0 + rr;
+        if (m >= nb && m < rows && c < nb) {
+            float* dst = C + (int64_t)m * ldc + c;
+            const float4 v = make_float4(Xs[rr * SOLVE_LD + c], Xs[rr * SOLVE_LD + c + 1], Xs[rr * SOLVE_LD + c + 2],
+                                         Xs[rr * SOLVE_LD + c + 3]);
+            if (vec && c + 3 < nb) {
+                *reinterpret_cast<float4*>(dst) = v;
+            } else {
+                dst[0] = v.x;
+                if (c + 1 < nb) dst[1] = v.y;
+                if (c + 2 < nb) dst[2] = v.z;
+                if (c + 3 < nb) dst[3] = v.w;
+            }
+        }
+    }
 }
 
 }  // namespace pb

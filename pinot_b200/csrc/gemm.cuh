@@ -34,7 +34,16 @@ struct GemmParams {
     int* post_info = nullptr;
     int post_nb = 0;
     int post_c0 = 0;
+    // Fused panel solve (tensor-core kernel only): once that factor is published through
+    // *post_flag, every CTA of tile column 0 multiplies its rows of the next panel (columns
+    // [0, post_nb) of C, rows >= post_nb) by L11^{-T} in place, which replaces the separate
+    // panel-TRSM launch of the next sweep step.
+    int* post_flag = nullptr;
+    int post_solve = 0;
 };
+
+// True when gemm() dispatches to the tcgen05 kernel (PINOT_B200_GEMM != "ffma").
+bool gemm_uses_tensor_cores();
 
 // Launches the GEMM on `stream`.  Returns PB_OK or an error code (message via set_error).
 int gemm(const GemmParams& p, cudaStream_t stream);

@@ -18,6 +18,7 @@ struct KParams {
     int lower, mirror, ktri, splitk;
     int vecA, vecB, vecC;
     float* post_wdiag; float* post_winv; int* post_info; int post_nb, post_c0;
+    int* post_flag; int post_solve;
 };
 
 // gemm_tc.cu: 3xTF32 tensor-core (tcgen05 / TMEM) implementation of the same contract.

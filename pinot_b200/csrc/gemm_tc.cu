@@ -22,8 +22,17 @@
 //     epilogue as the FFMA kernel (alpha/beta, bias, tanh, rank-1 term, lower/mirror masks,
 //     split-K atomics, Cholesky look-ahead).
 #include "gemm_params.cuh"
-#include "chol_diag.cuh"
 
+namespace pb {
+
+#ifdef PB_DEBUG_TIMING
+__device__ unsigned long long g_dbg_times[16];
+#define PB_STAMP(i) do { if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); g_dbg_times[i] = t_; } } while (0)
+#else
+#define PB_STAMP(i)
+#endif
+}  // namespace pb
+#include "chol_diag.cuh"
 namespace pb {
 
 namespace {
@@ -37,7 +46,7 @@ constexpr int KC_PER_STAGE = TK / 4;           // 16-byte K chunks per stage
 constexpr int OPERAND_BYTES = KC_PER_STAGE * LBO_BYTES;          // one of A_hi, A_lo, B_hi, B_lo
 constexpr int STAGE_BYTES = 4 * OPERAND_BYTES;
 constexpr int PIPE_BYTES = STAGES * STAGE_BYTES;
-constexpr int DIAG_BYTES = DIAG_SMEM_FLOATS * 4;
+constexpr int DIAG_BYTES = (DIAG_SMEM_FLOATS > SOLVE_SMEM_FLOATS ? DIAG_SMEM_FLOATS : SOLVE_SMEM_FLOATS) * 4;
 constexpr int DYN_SMEM_BYTES = (PIPE_BYTES > DIAG_BYTES ? PIPE_BYTES : DIAG_BYTES) + 128;
 constexpr int EPI_LD = 36;                     // floats per row of a warp's 32x32 epilogue staging tile
 constexpr int TMEM_COLS = 256;                // [0,128): hi.hi accumulator, [128,256): cross terms
@@ -200,7 +209,116 @@ __device__ __forceinline__ void tc_store_rowcontig(uint8_t* hi, uint8_t* lo, con
     }
 }
 
-template <bool TA, bool TB>
+// Writes one warp's 32 x 32 block (staged row-major in `tile`) to C.  EPI selects how much code is
+// instantiated -- the epilogue runs once per tile, straight-line, and its instruction footprint is
+// what it costs: 0 = alpha/beta/bias (+ lower mask); 1 = 0 + tanh; 2 = 0 + rank-1 term + mirror;
+// 3 = everything incl. split-K atomics and unaligned C, as one compact scalar loop.
+template <int EPI>
+__device__ __forceinline__ void epilogue_rows(const KParams& p, const float* tile, float alpha, float beta, float r1c,
+                                              bool last_chunk, int m0, int n0, int q, int c0, int lane) {
+    const int c4 = (lane & 7) * 4;
+    const int n = n0 + c0 + c4;
+    if constexpr (EPI != 3) {
+        // all C reads first (one L2 round trip), then 8 x {combine, store}
+        float4 cold[8];
+#pragma unroll
+        for (int t8 = 0; t8 < 8; ++t8) {
+            const int m = m0 + q * 32 + t8 * 4 + (lane >> 3);
+            cold[t8] = make_float4(0.f, 0.f, 0.f, 0.f);
+            // (on diagonal tiles of a `lower` update this also reads a few elements above the
+            //  diagonal: harmless, they are never stored)
+            if (beta != 0.f && m < p.M && n + 3 < p.N)
+                cold[t8] = *reinterpret_cast<const float4*>(p.C + (int64_t)m * p.ldc + n);
+        }
+        float4 bv = make_float4(0.f, 0.f, 0.f, 0.f), rv = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (last_chunk && n + 3 < p.N) {
+            if (p.bias) bv = make_float4(__ldg(p.bias + n), __ldg(p.bias + n + 1), __ldg(p.bias + n + 2), __ldg(p.bias + n + 3));
+            if (EPI == 2 && p.r1u) rv = make_float4(__ldg(p.r1v + n), __ldg(p.r1v + n + 1), __ldg(p.r1v + n + 2), __ldg(p.r1v + n + 3));
+        }
+#pragma unroll
+        for (int t8 = 0; t8 < 8; ++t8) {
+            const int rl = t8 * 4 + (lane >> 3);
+            const int m = m0 + q * 32 + rl;
+            if (m >= p.M || n >= p.N) continue;
+            const float4 acc = *reinterpret_cast<const float4*>(tile + rl * EPI_LD + c4);
+            float* cp = p.C + (int64_t)m * p.ldc + n;
+            if (n + 3 < p.N) {
+                float4 o;
+                o.x = fmaf(alpha, acc.x, fmaf(beta, cold[t8].x, bv.x));
+                o.y = fmaf(alpha, acc.y, fmaf(beta, cold[t8].y, bv.y));
+                o.z = fmaf(alpha, acc.z, fmaf(beta, cold[t8].z, bv.z));
+                o.w = fmaf(alpha, acc.w, fmaf(beta, cold[t8].w, bv.w));
+                if (EPI == 2 && last_chunk && p.r1u) {
+                    const float um = __ldg(p.r1u + m) * r1c;
+                    o.x = fmaf(um, rv.x, o.x); o.y = fmaf(um, rv.y, o.y);
+                    o.z = fmaf(um, rv.z, o.z); o.w = fmaf(um, rv.w, o.w);
+                }
+                if (EPI == 1 && last_chunk && p.act == 1) {
+                    o.x = tanhf(o.x); o.y = tanhf(o.y); o.z = tanhf(o.z); o.w = tanhf(o.w);
+                }
+                if (EPI == 2 && last_chunk && p.mirror) {
+                    if (n + 0 < m) p.C[(int64_t)(n + 0) * p.ldc + m] = o.x;
+                    if (n + 1 < m) p.C[(int64_t)(n + 1) * p.ldc + m] = o.y;
+                    if (n + 2 < m) p.C[(int64_t)(n + 2) * p.ldc + m] = o.z;
+                    if (n + 3 < m) p.C[(int64_t)(n + 3) * p.ldc + m] = o.w;
+                }
+                if (!p.lower || n + 3 <= m) {
+                    *reinterpret_cast<float4*>(cp) = o;
+                } else {
+                    if (n + 0 <= m) cp[0] = o.x;
+                    if (n + 1 <= m) cp[1] = o.y;
+                    if (n + 2 <= m) cp[2] = o.z;
+                }
+            } else {
+                const float a4[4] = {acc.x, acc.y, acc.z, acc.w};
+#pragma unroll 1
+                for (int j = 0; j < 4; ++j) {
+                    if (n + j < p.N && (!p.lower || n + j <= m)) {
+                        float o = alpha * a4[j];
+                        if (beta != 0.f) o = fmaf(beta, cp[j], o);
+                        if (last_chunk) {
+                            if (p.bias) o += __ldg(p.bias + n + j);
+                            if (EPI == 2 && p.r1u) o = fmaf(__ldg(p.r1u + m) * r1c, __ldg(p.r1v + n + j), o);
+                            if (EPI == 1 && p.act == 1) o = tanhf(o);
+                        }
+                        cp[j] = o;
+                        if (EPI == 2 && last_chunk && p.mirror && n + j < m) p.C[(int64_t)(n + j) * p.ldc + m] = o;
+                    }
+                }
+            }
+        }
+    } else {
+#pragma unroll 1
+        for (int t8 = 0; t8 < 8; ++t8) {
+            const int rl = t8 * 4 + (lane >> 3);
+            const int m = m0 + q * 32 + rl;
+            if (m >= p.M || n >= p.N) continue;
+            const float4 acc = *reinterpret_cast<const float4*>(tile + rl * EPI_LD + c4);
+            const float a4[4] = {acc.x, acc.y, acc.z, acc.w};
+            float* cp = p.C + (int64_t)m * p.ldc + n;
+            const float um = (last_chunk && p.r1u) ? __ldg(p.r1u + m) * r1c : 0.f;
+#pragma unroll 1
+            for (int j = 0; j < 4; ++j) {
+                if (n + j >= p.N || (p.lower && n + j > m)) continue;
+                float o = alpha * a4[j];
+                if (p.splitk > 1) {
+                    atomicAdd(cp + j, o);
+                    continue;
+                }
+                if (beta != 0.f) o = fmaf(beta, cp[j], o);
+                if (last_chunk) {
+                    if (p.bias) o += __ldg(p.bias + n + j);
+                    if (p.r1u) o = fmaf(um, __ldg(p.r1v + n + j), o);
+                    if (p.act == 1) o = tanhf(o);
+                }
+                cp[j] = o;
+                if (p.mirror && last_chunk && n + j < m) p.C[(int64_t)(n + j) * p.ldc + m] = o;
+            }
+        }
+    }
+}
+
+template <bool TA, bool TB, int EPI, bool POST>
 __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
     extern __shared__ __align__(128) uint8_t dyn_smem[];
     __shared__ __align__(8) uint64_t mma_bar[STAGES];
@@ -221,6 +339,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
     }
     const int num_k = (ke > kb) ? (ke - kb + TK - 1) / TK : 0;
 
+    PB_STAMP(0);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dyn_smem) + 127) & ~(uintptr_t)127);
 
@@ -240,6 +359,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_d = tmem_base_holder;
+    PB_STAMP(1);
 
     // MMA N: the valid columns of this tile rounded up to a legal UMMA N (multiple of 16)
     const int n_valid = min(TN, p.N - n0);
@@ -311,6 +431,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
             mbar_wait(&mma_bar[last % STAGES], (uint32_t)((last / STAGES) & 1));
         }
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        PB_STAMP(2);
 
         // ------------- epilogue / flush: TMEM -> registers -> global -------------
         // chunk 0 applies beta; later chunks accumulate onto C; bias / rank-1 / activation / mirror
@@ -343,6 +464,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
                     : "r"(taddr + 128u)
                     : "memory");
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (cc == 0) PB_STAMP(11);
             } else {
 #pragma unroll
                 for (int j = 0; j < 32; ++j) { v[j] = 0u; w[j] = 0u; }
@@ -360,59 +482,11 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
                 *reinterpret_cast<float4*>(tile + lane * EPI_LD + 4 * i) = t;
             }
             __syncwarp();
-#pragma unroll 2
-            for (int t8 = 0; t8 < 8; ++t8) {
-                const int rl = t8 * 4 + (lane >> 3);
-                const int c4 = (lane & 7) * 4;
-                const int m = m0 + q * 32 + rl;
-                const int n = n0 + c0 + c4;
-                if (m >= p.M || n >= p.N) continue;
-                const float4 acc = *reinterpret_cast<const float4*>(tile + rl * EPI_LD + c4);
-                float o[4] = {alpha * acc.x, alpha * acc.y, alpha * acc.z, alpha * acc.w};
-                float* cp = p.C + (int64_t)m * p.ldc + n;
-                if (p.splitk > 1) {
-#pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        if (n + j < p.N && (!p.lower || n + j <= m)) atomicAdd(cp + j, o[j]);
-                    continue;
-                }
-                const bool full = (n + 3 < p.N) && (!p.lower || n + 3 <= m);
-                if (beta != 0.f) {
-                    if (full && p.vecC) {
-                        const float4 c = *reinterpret_cast<const float4*>(cp);
-                        o[0] = fmaf(beta, c.x, o[0]); o[1] = fmaf(beta, c.y, o[1]);
-                        o[2] = fmaf(beta, c.z, o[2]); o[3] = fmaf(beta, c.w, o[3]);
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 4; ++j)
-                            if (n + j < p.N && (!p.lower || n + j <= m)) o[j] = fmaf(beta, cp[j], o[j]);
-                    }
-                }
-                if (last_chunk) {
-                    const float um = p.r1u ? __ldg(p.r1u + m) * r1c : 0.f;
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        if (n + j < p.N) {
-                            if (p.bias) o[j] += __ldg(p.bias + n + j);
-                            if (p.r1u) o[j] = fmaf(um, __ldg(p.r1v + n + j), o[j]);
-                            if (p.act == 1) o[j] = tanhf(o[j]);
-                        }
-                    }
-                }
-                if (full && p.vecC) {
-                    *reinterpret_cast<float4*>(cp) = make_float4(o[0], o[1], o[2], o[3]);
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        if (n + j < p.N && (!p.lower || n + j <= m)) cp[j] = o[j];
-                }
-                if (p.mirror && last_chunk) {
-#pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        if (n + j < p.N && n + j < m) p.C[(int64_t)(n + j) * p.ldc + m] = o[j];
-                }
-            }
+            if (cc == 0) PB_STAMP(12);
+            epilogue_rows<EPI>(p, tile, alpha, beta, r1c, last_chunk, m0, n0, q, c0, lane);
             __syncwarp();
+            if (cc == 0) PB_STAMP(13);
+            if (cc == 32) PB_STAMP(14);
         }
         // all warps have drained the accumulators before the next chunk overwrites them
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -420,21 +494,43 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     }
 
+    PB_STAMP(3);
     // ---- teardown: every warp is done reading TMEM (synchronised above) before warp 0 frees it ----
     if (warp == 0) {
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)TMEM_COLS)
                      : "memory");
     }
 
-    // ---------------- Cholesky look-ahead (tile (0,0) only) ----------------
-    if (p.post_wdiag != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {
-        const int fail = factor_diag_block_regs(p.C, p.ldc, 0, p.post_nb, /*coherent=*/true,
-                                                reinterpret_cast<float*>(smem), p.post_wdiag, p.post_winv);
-        if (fail >= 0 && threadIdx.x == 0 && p.post_info) atomicCAS(p.post_info, 0, p.post_c0 + fail + 1);
+    // ---------------- Cholesky look-ahead and fused panel solve (tile column 0) ----------------
+    if (POST && p.post_wdiag != nullptr && blockIdx.x == 0 && blockIdx.z == 0) {
+        float* fsmem = reinterpret_cast<float*>(smem);
+        const bool owner = (blockIdx.y == 0);
+        PB_STAMP(4);
+        if (owner) {
+            // tile (0,0): factor the next diagonal block while the other tiles are still running
+            const int fail = factor_diag_block_regs(p.C, p.ldc, 0, p.post_nb, /*coherent=*/true, fsmem,
+                                                    p.post_wdiag, p.post_winv);
+            if (fail >= 0 && threadIdx.x == 0 && p.post_info) atomicCAS(p.post_info, 0, p.post_c0 + fail + 1);
+            PB_STAMP(5);
+            if (p.post_flag) publish_flag(p.post_flag);
+            PB_STAMP(6);
+        }
+        if (p.post_solve) {
+            if (!owner) wait_flag(p.post_flag);
+            else __syncthreads();
+            panel_solve_tile(p.C, p.ldc, m0, p.M, p.post_nb, p.post_winv, fsmem);
+            PB_STAMP(7);
+        }
     }
 }
 
 }  // namespace
+
+#ifdef PB_DEBUG_TIMING
+extern "C" __attribute__((visibility("default"))) int pinot_b200_debug_times(unsigned long long* out16) {
+    return (int)cudaMemcpyFromSymbol(out16, g_dbg_times, sizeof(unsigned long long) * 16);
+}
+#endif
 
 int launch_gemm_tc(const KParams& p, bool transA, bool transB, dim3 grid, cudaStream_t stream) {
     auto launch = [&](auto kern) -> int {
@@ -442,10 +538,23 @@ int launch_gemm_tc(const KParams& p, bool transA, bool transB, dim3 grid, cudaSt
         kern<<<grid, NTHREADS, DYN_SMEM_BYTES, stream>>>(p);
         return check_launch("gemm (tcgen05)");
     };
-    if (!transA && !transB) return launch(tgemm_kernel<false, false>);
-    if (!transA && transB) return launch(tgemm_kernel<false, true>);
-    if (transA && !transB) return launch(tgemm_kernel<true, false>);
-    return launch(tgemm_kernel<true, true>);
+    // epilogue variant (see epilogue_rows): the generic one whenever a specialised one is not built
+    int epi = 0;
+    if (p.splitk > 1 || !p.vecC) epi = 3;
+    else if (p.r1u || p.mirror) epi = (!transA && transB) ? 2 : 3;
+    else if (p.act) epi = (!transA) ? 1 : 3;
+    if (p.post_wdiag) {
+        PB_REQUIRE(!transA && transB && epi == 0, "gemm: the Cholesky look-ahead is built for the NT update only");
+        return launch(tgemm_kernel<false, true, 0, true>);
+    }
+#define PB_TC(TA_, TB_, E_) return launch(tgemm_kernel<TA_, TB_, E_, false>)
+    if (!transA && !transB) { if (epi == 0) PB_TC(false, false, 0); if (epi == 1) PB_TC(false, false, 1); PB_TC(false, false, 3); }
+    if (!transA && transB)  { if (epi == 0) PB_TC(false, true, 0);  if (epi == 1) PB_TC(false, true, 1);
+                              if (epi == 2) PB_TC(false, true, 2);  PB_TC(false, true, 3); }
+    if (transA && !transB)  { if (epi == 0) PB_TC(true, false, 0);  PB_TC(true, false, 3); }
+    if (epi == 0) PB_TC(true, true, 0);
+    PB_TC(true, true, 3);
+#undef PB_TC
 }
 
 }  // namespace pb
