@@ -61,6 +61,12 @@ PINOT_B200_API int pinot_b200_mp_csr_aggregate_bwd(const float* dout, float* dx,
                                     const float* dst_scale, int64_t n_src, int64_t feat,
                                     cudaStream_t stream);
 
+/* Row gather out[i,:] = x[idx[i],:] (idx: int64, device).  The data movement of re-batching a
+ * selection of molecules, i.e. of dgl.batch([dgl.unbatch(g)[i] for i in idxs]) in
+ * pinot/active/experiment.py:83-104 (_slice_fn_graph). */
+PINOT_B200_API int pinot_b200_gather_rows(const float* x, const int64_t* idx, float* out, int64_t n_out,
+                                          int64_t feat, cudaStream_t stream);
+
 /* Readout: out[g,:] = sum (or mean) of x[n,:] over the nodes n in [offsets[g], offsets[g+1]).
  * Replaces dgl.sum_nodes(g, "h") at pinot/representation/sequential.py:78,92-103. */
 PINOT_B200_API int pinot_b200_segment_readout_fwd(const float* x, float* out, const int32_t* offsets,

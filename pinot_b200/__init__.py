@@ -10,6 +10,8 @@ from . import representation  # noqa: F401
 from . import regressors  # noqa: F401
 from . import net  # noqa: F401
 from . import synthetic  # noqa: F401
+from . import active  # noqa: F401
+from . import distributed  # noqa: F401
 from .net import Net  # noqa: F401
 from .graph import BatchedGraph, batch, unbatch, sum_nodes  # noqa: F401
 

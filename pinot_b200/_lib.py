@@ -24,6 +24,7 @@ SIGNATURES = {
     "pinot_b200_launch_count": [],
     "pinot_b200_mp_csr_aggregate_fwd": [_ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i64, _ptr],
     "pinot_b200_mp_csr_aggregate_bwd": [_ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i64, _ptr],
+    "pinot_b200_gather_rows": [_ptr, _ptr, _ptr, _i64, _i64, _ptr],
     "pinot_b200_segment_readout_fwd": [_ptr, _ptr, _ptr, _i64, _i64, _i32, _ptr],
     "pinot_b200_segment_readout_bwd": [_ptr, _ptr, _ptr, _ptr, _i64, _i64, _i32, _ptr],
     "pinot_b200_node_update_fwd": [_ptr, _ptr, _ptr, _ptr, _i64, _i64, _i64, _i32, _i32, _i32, _ptr],

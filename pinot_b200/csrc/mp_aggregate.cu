@@ -207,6 +207,24 @@ segment_readout_bwd_kernel(const float* __restrict__ dout, float* __restrict__ d
     }
 }
 
+// out[i, :] = x[idx[i], :]  (row gather: the feature / embedding side of re-batching a selection of
+// molecules out of a device-resident pool)
+template <int VEC>
+__global__ void __launch_bounds__(256)
+gather_rows_kernel(const float* __restrict__ x, const int64_t* __restrict__ idx, float* __restrict__ out,
+                   int64_t n_out, int feat_v) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t i = t / feat_v;
+    if (i >= n_out) return;
+    const int c = (int)(t - i * feat_v);
+    const int64_t j = __ldg(idx + i);
+    if (VEC == 4) {
+        *reinterpret_cast<float4*>(out + (i * feat_v + c) * 4) = pb::ldg4(x + (j * feat_v + c) * 4);
+    } else {
+        out[i * feat_v + c] = __ldg(x + j * feat_v + c);
+    }
+}
+
 inline bool can_vec4(int64_t feat, const void* a, const void* b) {
     return (feat % 4 == 0) && pb::aligned16(a) && pb::aligned16(b);
 }
@@ -273,6 +291,21 @@ int pinot_b200_mp_csr_aggregate_bwd(const float* dout, float* dx, const int32_t*
     // transposed CSR with the two scale vectors trading places.
     return launch_aggregate(dout, dx, indptr_t, indices_t, dst_scale, src_scale, n_src, feat, stream,
                             "mp_csr_aggregate_bwd");
+}
+
+int pinot_b200_gather_rows(const float* x, const int64_t* idx, float* out, int64_t n_out, int64_t feat,
+                           cudaStream_t stream) {
+    PB_REQUIRE(n_out >= 0 && feat > 0, "gather_rows: invalid sizes");
+    if (n_out == 0) return pb::PB_OK;
+    PB_REQUIRE(x && idx && out, "gather_rows: null pointer");
+    if (can_vec4(feat, x, out)) {
+        const int fv = (int)(feat / 4);
+        gather_rows_kernel<4><<<(unsigned)pb::ceil_div(n_out * fv, 256), 256, 0, stream>>>(x, idx, out, n_out, fv);
+    } else {
+        gather_rows_kernel<1><<<(unsigned)pb::ceil_div(n_out * feat, 256), 256, 0, stream>>>(x, idx, out, n_out,
+                                                                                         (int)feat);
+    }
+    return pb::check_launch("gather_rows");
 }
 
 int pinot_b200_segment_readout_fwd(const float* x, float* out, const int32_t* offsets,

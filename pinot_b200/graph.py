@@ -97,6 +97,7 @@ class BatchedGraph:
         self.ndata = _Frame(self, lambda: self._num_nodes)
         self.edata = _Frame(self, lambda: int(self._src.numel()))
         self._csr = None
+        self._off = None
 
     # -- construction in the style of pinot/graph.py:208-239 -----------------------------------
     def add_nodes(self, n):
@@ -105,6 +106,7 @@ class BatchedGraph:
         self._num_nodes += int(n)
         self._bnn = [self._num_nodes]
         self._csr = None
+        self._off = None
 
     def add_edges(self, u, v, data=None):
         if len(self._bnn) != 1:
@@ -133,6 +135,7 @@ class BatchedGraph:
                     pad = torch.zeros((n_old,) + tuple(new.shape[1:]), dtype=new.dtype)
                     dict.__setitem__(self.edata, k, torch.cat([pad, new], dim=0))
         self._csr = None
+        self._off = None
 
     # -- DGL surface ----------------------------------------------------------------------------
     @property
@@ -185,6 +188,7 @@ class BatchedGraph:
         for k, v in self.edata.items():
             dict.__setitem__(g.edata, k, v.to(device) if torch.is_tensor(v) else v)
         g._csr = self._csr if (self._csr is not None and torch.device(device) == self._src.device) else None
+        g._off = None
         return g
 
     @contextlib.contextmanager
@@ -208,11 +212,70 @@ class BatchedGraph:
         return "BatchedGraph(batch_size=%d, num_nodes=%d, num_edges=%d, device=%s)" % (
             self.batch_size, self._num_nodes, self.number_of_edges(), self.device)
 
+    # -- selection ------------------------------------------------------------------------------
+    def _offsets(self):
+        """(node offsets, edge offsets) per graph as int64 tensors on the graph's device (cached)."""
+        if getattr(self, "_off", None) is None or self._off[0].device != self._src.device:
+            dev = self._src.device
+            bnn = torch.tensor(self._bnn, dtype=torch.long)
+            bne = torch.tensor(self._bne, dtype=torch.long)
+            noff = torch.zeros(len(self._bnn) + 1, dtype=torch.long)
+            eoff = torch.zeros(len(self._bne) + 1, dtype=torch.long)
+            noff[1:] = torch.cumsum(bnn, 0)
+            eoff[1:] = torch.cumsum(bne, 0)
+            self._off = (noff.to(dev), eoff.to(dev))
+        return self._off
+
+    def select(self, idxs):
+        """``dgl.batch([dgl.unbatch(self)[i] for i in idxs])`` without materialising the individual
+        graphs (pinot/active/experiment.py:83-104 re-batches like this every acquisition round):
+        index arithmetic on the device, node / edge data moved by the row-gather kernel."""
+        dev = self._src.device
+        idx_host = [int(i) for i in (idxs.tolist() if torch.is_tensor(idxs) else idxs)]
+        nb = len(self._bnn)
+        idx_host = [i + nb if i < 0 else i for i in idx_host]
+        if any(i < 0 or i >= nb for i in idx_host):
+            raise IndexError("graph index out of range")
+        if not idx_host:
+            raise ValueError("select() needs at least one graph")
+        idx = torch.tensor(idx_host, dtype=torch.long, device=dev)
+        noff, eoff = self._offsets()
+        cn = noff[idx + 1] - noff[idx]                      # nodes per selected graph
+        ce = eoff[idx + 1] - eoff[idx]
+        new_noff = torch.zeros(len(idx_host) + 1, dtype=torch.long, device=dev)
+        new_eoff = torch.zeros_like(new_noff)
+        new_noff[1:] = torch.cumsum(cn, 0)
+        new_eoff[1:] = torch.cumsum(ce, 0)
+        bnn = [self._bnn[i] for i in idx_host]
+        bne = [self._bne[i] for i in idx_host]
+        n_new, e_new = sum(bnn), sum(bne)
+        # source position of every new node / edge
+        which_n = torch.repeat_interleave(torch.arange(len(idx_host), device=dev), cn, output_size=n_new)
+        node_src = torch.arange(n_new, device=dev) - new_noff[which_n] + noff[idx][which_n]
+        which_e = torch.repeat_interleave(torch.arange(len(idx_host), device=dev), ce, output_size=e_new)
+        edge_src = torch.arange(e_new, device=dev) - new_eoff[which_e] + eoff[idx][which_e]
+        shift = (new_noff[:-1] - noff[idx])[which_e]        # old node id -> new node id, per edge
+        out = BatchedGraph(self._src[edge_src] + shift, self._dst[edge_src] + shift, n_new, bnn, bne, validate=False)
+        for name, frame, index in (("ndata", self.ndata, node_src), ("edata", self.edata, edge_src)):
+            for k, v in frame.items():
+                dict.__setitem__(getattr(out, name), k, _gather_rows(v, index))
+        return out
+
     # -- kernel view ----------------------------------------------------------------------------
     def csr(self):
         if self._csr is None:
             self._csr = GraphCSR(self._src, self._dst, self._num_nodes, self._bnn)
         return self._csr
+
+
+def _gather_rows(v, index):
+    """v[index] along dim 0; fp32 CUDA matrices go through the library's row-gather kernel."""
+    if v.is_cuda and v.dtype == torch.float32 and v.dim() == 2 and v.is_contiguous():
+        from ._lib import call, ptr
+        out = torch.empty((index.numel(), v.shape[1]), device=v.device, dtype=torch.float32)
+        call("gather_rows", ptr(v), ptr(index), ptr(out), index.numel(), v.shape[1])
+        return out
+    return v[index]
 
 
 def batch(graphs):

@@ -82,12 +82,27 @@ class Net(BaseNet):
             sampler.sample_params()
         return self._condition(h, *args, **kwargs)
 
-    def condition_marginal(self, g):
+    def condition_marginal(self, g, chunk_molecules=65536):
         """Per-molecule predictive ``Normal`` for an exact-GP head without the n_te x n_te
-        covariance (not in the reference API; equals ``pinot.metrics._independent(net.condition(g))``)."""
+        covariance (not in the reference API; equals ``pinot.metrics._independent(net.condition(g))``).
+        The training graphs are embedded and factored once; the graphs in ``g`` are embedded and
+        scored ``chunk_molecules`` at a time, so million-molecule pools fit."""
         if not self.has_exact_gp:
             raise NotImplementedError("condition_marginal is available for exact-GP heads only")
+        from . import ops
+        reg = self.output_regressor
         with torch.no_grad():
-            h = self.representation(g)
             h_last = self.representation(self.g_last)
-        return self.output_regressor.condition_marginal(h, x_tr=h_last, y_tr=self.y_last)
+            post = ops.ExactGPPosterior(h_last, self.y_last, reg.kernel.scale, reg.kernel.variance, reg.log_sigma,
+                                        kind=reg._kind(), check=reg.check_positive_definite)
+            nb = g.batch_size
+            means, variances = [], []
+            for lo in range(0, nb, chunk_molecules):
+                hi = min(nb, lo + chunk_molecules)
+                sub = g if (lo == 0 and hi == nb) else g.select(range(lo, hi))
+                m, v = post.mean_var(self.representation(sub))
+                means.append(m)
+                variances.append(v)
+        mean = torch.cat(means) if len(means) > 1 else means[0]
+        var = torch.cat(variances) if len(variances) > 1 else variances[0]
+        return torch.distributions.normal.Normal(loc=mean, scale=var.clamp_min(0).sqrt(), validate_args=False)

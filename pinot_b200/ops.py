@@ -348,6 +348,58 @@ def exact_gp_posterior(x_te, x_tr, y_tr, scale, variance, log_sigma, kind="rbf",
     return mean, cov
 
 
+class ExactGPPosterior:
+    """Training-set factorisation kept for repeated prediction: one sweep over
+    ``[K + (eps + sigma^2) I ; y^T ; I]`` gives ``z = L^-1 y`` and ``W = L^-T``; every later batch of
+    test points then costs one Gram launch, one GEMM ``V = K_te,tr W`` and one fused row reduction
+    (mean ``V z``, variance ``k** - |V_i|^2``) -- no n_te x n_te covariance, no second factorisation.
+    Equals the mean and the diagonal of the covariance of
+    pinot/regressors/gaussian_process_regressor.py:168-233, rectangular ``_perturb`` included."""
+
+    @torch.no_grad()
+    def __init__(self, x_tr, y_tr, scale, variance, log_sigma, kind="rbf", check=True):
+        self.kind = kind
+        self.x_tr = _f32c(x_tr.detach())
+        n = self.n = self.x_tr.shape[0]
+        dev = self.x_tr.device
+        self.scale = _f32c(scale.detach().reshape(-1))
+        self.variance = _f32c(variance.detach().reshape(1))
+        ls = _f32c(log_sigma.detach().reshape(1))
+        self.ld = ld = _pad4(n)
+        e = torch.zeros((2 * n + 1, ld), device=dev, dtype=torch.float32)
+        gram_raw(kind, self.x_tr, self.x_tr, self.scale, self.variance, out=e, ldo=ld, diag_add=EPSILON, diag_add_log=ls)
+        e[n, :n] = _f32c(y_tr.detach().reshape(-1))
+        e[n + 1:, :n].diagonal().fill_(1.0)
+        potrf_ext_raw(e, n, n_ext_dense=1, ext_identity=True, want_diag=False, check=check)
+        self.z = e[n, :n].clone()
+        self.linv_t = e[n + 1:]          # (n, ld) view: W = L^-T, upper triangular
+        self.alpha = torch.empty((n,), device=dev, dtype=torch.float32)   # (K + sigma^2 I)^-1 y = W z
+        call("gemv_rows", ptr(self.linv_t), ld, n, n, 1, ptr(self.z), ptr(self.alpha))
+        self._e = e
+
+    @torch.no_grad()
+    def mean_var(self, x_te, chunk=32768):
+        """Predictive mean and marginal variance, (n_te,) each, computed ``chunk`` test points at a time."""
+        x_te = _f32c(x_te.detach())
+        nte, n, dev = x_te.shape[0], self.n, x_te.device
+        mean = torch.empty((nte,), device=dev, dtype=torch.float32)
+        var = torch.empty((nte,), device=dev, dtype=torch.float32)
+        for r0 in range(0, nte, chunk):
+            r1 = min(nte, r0 + chunk)
+            g = gram_raw(self.kind, x_te[r0:r1], self.x_tr, self.scale, self.variance)
+            if r0 < n:   # _perturb of the rectangular K_te,tr: eps on its main diagonal (:95)
+                g.diagonal(offset=r0).add_(EPSILON)
+            v = torch.empty((r1 - r0, n), device=dev, dtype=torch.float32)
+            call("sgemm", 0, 0, r1 - r0, n, n, 1.0, ptr(g), n, ptr(self.linv_t), self.ld, 0.0, ptr(v), n)
+            # variance from V (the mean V z of the same pass is discarded: the mean is taken as
+            # K_te,tr alpha in plain fp32, exactly the reference's expression at :212)
+            scratch = torch.empty((r1 - r0,), device=dev, dtype=torch.float32)
+            call("gp_predict_mean_var", ptr(v), n, r1 - r0, n, ptr(self.z), ptr(self.variance), EPSILON,
+                 ptr(scratch), ptr(var[r0:r1]))
+            call("gemv_rows", ptr(g), n, r1 - r0, n, 0, ptr(self.alpha), ptr(mean[r0:r1]))
+        return mean, var
+
+
 class _CholSolve(torch.autograd.Function):
     """(K, B) -> (L, X = L^-1 B) with K = L L^T; differentiable (generic Cholesky backward built
     from L^-T, which the same sweep provides).  Used by the variational GP

@@ -112,3 +112,26 @@ def test_synthetic_shape_statistics():
     assert 51.0 < g.number_of_edges() / 2000 < 57.0
     g2, y2 = synthetic.make_batch(2000, seed=2666)
     assert torch.equal(g.edges()[0], g2.edges()[0]) and torch.equal(y, y2)
+
+
+def test_select_equals_unbatch_then_batch():
+    """BatchedGraph.select == dgl.batch([dgl.unbatch(g)[i] for i in idxs]) bit for bit
+    (pinot/active/experiment.py:83-104), checked against the oracle's unbatch / batch."""
+    g, _ = synthetic.make_batch(40, seed=8)
+    ref = dgl_ref.from_arrays(*g.edges(), g.number_of_nodes(), g.batch_num_nodes().tolist(),
+                              g.batch_num_edges().tolist(), ndata={"h": g.ndata["h"]})
+    ref_parts = dgl_ref.unbatch(ref)
+    for idxs in ([5], [39, 0, 17, 17, 3], list(range(40)), list(range(10, 20))):
+        got = g.select(idxs)
+        want = dgl_ref.batch([ref_parts[i] for i in idxs])
+        assert got.edges()[0].tolist() == want.src and got.edges()[1].tolist() == want.dst
+        assert got.batch_num_nodes().tolist() == want.batch_nodes
+        assert got.batch_num_edges().tolist() == want.batch_edges
+        assert torch.equal(got.ndata["h"], want.ndata["h"])
+    with pytest.raises(IndexError):
+        g.select([40])
+    from pinot_b200 import active
+    gs, ys = active.slice_fn_tuple((g, torch.arange(40.0)[:, None]), [3, 1])
+    assert gs.batch_size == 2 and ys.flatten().tolist() == [3.0, 1.0]
+    with pytest.raises(RuntimeError, match="more than one"):
+        active.slice_fn_graph(g.select([0]), [0])
