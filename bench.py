@@ -39,6 +39,7 @@ def parse():
     ap.add_argument("--molecules", type=int, default=N_MOL)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-fit16k", action="store_true")
     return ap.parse_args()
 
 
@@ -332,6 +333,40 @@ def b200_main(args):
                "d2h_bytes_per_step": 4, "ms_per_step": 1e3 * e2e_s / args.steps,
                "includes": "H2D of edges/features/targets from pinned memory, CSR build, train step, loss.item()"}
 
+    # ---- second headline number of BASELINE.json: exact-GP fit at N = 16 384 (embeddings given):
+    #      Gram + sweep (factor, L^-1 y, L^-T) + NLL + closed-form gradients, one GPU ----
+    fit16k = None
+    if rank == 0 and not args.no_fit16k:
+        from pinot_b200 import ops
+        n16, d16 = 16384, HIDDEN
+        gen = torch.Generator(device="cpu").manual_seed(0)
+        x16 = (0.1 * torch.randn(n16, d16, generator=gen)).to(dev).requires_grad_(True)
+        y16 = torch.randn(n16, 1, generator=gen).to(dev)
+        sc16 = torch.zeros(d16, device=dev, requires_grad=True)
+        var16 = torch.zeros((), device=dev, requires_grad=True)
+        ls16 = torch.tensor(-3.0, device=dev, requires_grad=True)
+
+        def fit():
+            for t in (x16, sc16, var16, ls16):
+                t.grad = None
+            ops.exact_gp_loss(x16, y16, sc16, var16, ls16).sum().backward()
+
+        fit()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(3):
+            flush_buf.zero_()
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            fit()
+            e.record()
+            torch.cuda.synchronize()
+            ts.append(s.elapsed_time(e))
+        fit16k = {"value": sorted(ts)[1], "unit": "ms", "n": n16, "d": d16,
+                  "what": "Gram + Cholesky sweep with L^-1 y and L^-T + NLL + gradients w.r.t. embeddings and "
+                          "hyper-parameters, fp32 (3xTF32 tensor-core updates), 1 GPU"}
+        del x16, y16
+
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         v, ms, cores, sample = cpu_arm(n_mol, steps=2, warmup=1, budget_s=40.0)
@@ -344,7 +379,7 @@ def b200_main(args):
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(n_mol, world),
             "roofline": roofline, "roofline_other_kernels": extra, "kernel_shares": shares,
-            "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+            "exact_gp_fit_n16k": fit16k, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
             "final_loss": final_loss,
         }
         print(json.dumps(line))
