@@ -366,19 +366,33 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
     const int n_mma = min(TN, ((n_valid + 15) / 16) * 16);
     const uint32_t idesc = make_idesc(n_mma);
 
-    float4 ra[2], rb[2];
-    auto gload = [&](int k0) {
-        if (TA) tc_load_rowcontig(p.A, p.lda, p.M, ke, m0, k0, p.vecA, p.kscale, ra);
-        else    tc_load_kcontig(p.A, p.lda, p.M, ke, m0, k0, p.vecA, p.kscale, ra);
-        if (TB) tc_load_kcontig(p.B, p.ldb, p.N, ke, n0, k0, p.vecB, nullptr, rb);
-        else    tc_load_rowcontig(p.B, p.ldb, p.N, ke, n0, k0, p.vecB, nullptr, rb);
+    // two register images per operand: two K-slabs are in flight while a third is being split
+    float4 ra0[2], rb0[2], ra1[2], rb1[2];
+    auto gload0 = [&](int k0) {
+        if (TA) tc_load_rowcontig(p.A, p.lda, p.M, ke, m0, k0, p.vecA, p.kscale, ra0);
+        else    tc_load_kcontig(p.A, p.lda, p.M, ke, m0, k0, p.vecA, p.kscale, ra0);
+        if (TB) tc_load_kcontig(p.B, p.ldb, p.N, ke, n0, k0, p.vecB, nullptr, rb0);
+        else    tc_load_rowcontig(p.B, p.ldb, p.N, ke, n0, k0, p.vecB, nullptr, rb0);
     };
-    auto sstore = [&](int stage) {
+    auto gload1 = [&](int k0) {
+        if (TA) tc_load_rowcontig(p.A, p.lda, p.M, ke, m0, k0, p.vecA, p.kscale, ra1);
+        else    tc_load_kcontig(p.A, p.lda, p.M, ke, m0, k0, p.vecA, p.kscale, ra1);
+        if (TB) tc_load_kcontig(p.B, p.ldb, p.N, ke, n0, k0, p.vecB, nullptr, rb1);
+        else    tc_load_rowcontig(p.B, p.ldb, p.N, ke, n0, k0, p.vecB, nullptr, rb1);
+    };
+    auto sstore0 = [&](int stage) {
         uint8_t* base = smem + stage * STAGE_BYTES;
-        if (TA) tc_store_rowcontig(base, base + OPERAND_BYTES, ra);
-        else    tc_store_kcontig(base, base + OPERAND_BYTES, ra);
-        if (TB) tc_store_kcontig(base + 2 * OPERAND_BYTES, base + 3 * OPERAND_BYTES, rb);
-        else    tc_store_rowcontig(base + 2 * OPERAND_BYTES, base + 3 * OPERAND_BYTES, rb);
+        if (TA) tc_store_rowcontig(base, base + OPERAND_BYTES, ra0);
+        else    tc_store_kcontig(base, base + OPERAND_BYTES, ra0);
+        if (TB) tc_store_kcontig(base + 2 * OPERAND_BYTES, base + 3 * OPERAND_BYTES, rb0);
+        else    tc_store_rowcontig(base + 2 * OPERAND_BYTES, base + 3 * OPERAND_BYTES, rb0);
+    };
+    auto sstore1 = [&](int stage) {
+        uint8_t* base = smem + stage * STAGE_BYTES;
+        if (TA) tc_store_rowcontig(base, base + OPERAND_BYTES, ra1);
+        else    tc_store_kcontig(base, base + OPERAND_BYTES, ra1);
+        if (TB) tc_store_kcontig(base + 2 * OPERAND_BYTES, base + 3 * OPERAND_BYTES, rb1);
+        else    tc_store_rowcontig(base + 2 * OPERAND_BYTES, base + 3 * OPERAND_BYTES, rb1);
     };
 
     // epilogue constants
@@ -393,7 +407,8 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
 
     const int tiles_per_chunk = KCHUNK / TK;
     const int num_chunks = num_k > 0 ? (num_k + tiles_per_chunk - 1) / tiles_per_chunk : 1;
-    if (num_k > 0) gload(kb);
+    if (num_k > 0) gload0(kb);
+    if (num_k > 1) gload1(kb + TK);
     for (int chunk = 0; chunk < num_chunks; ++chunk) {
         const int kt_beg = chunk * tiles_per_chunk;
         const int kt_end = min(num_k, kt_beg + tiles_per_chunk);
@@ -404,9 +419,16 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
                 // the MMAs that read this stage (slab kt - STAGES) must have completed
                 mbar_wait(&mma_bar[stage], (uint32_t)((kt / STAGES - 1) & 1));
             }
-            sstore(stage);
+            // slab kt lives in register image kt & 1; once it is in shared memory the image is refilled
+            // with slab kt + 2
+            if ((kt & 1) == 0) {
+                sstore0(stage);
+                if (kt + 2 < num_k) gload0(kb + (kt + 2) * TK);
+            } else {
+                sstore1(stage);
+                if (kt + 2 < num_k) gload1(kb + (kt + 2) * TK);
+            }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> tensor core
-            if (kt + 1 < num_k) gload(kb + (kt + 1) * TK);
             __syncthreads();
             if (tid == 0) {
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
