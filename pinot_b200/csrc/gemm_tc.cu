@@ -365,6 +365,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
     const int n_valid = min(TN, p.N - n0);
     const int n_mma = min(TN, ((n_valid + 15) / 16) * 16);
     const uint32_t idesc = make_idesc(n_mma);
+    const uint64_t desc_template = make_desc(0);
 
     // two register images per operand: two K-slabs are in flight while a third is being split
     float4 ra0[2], rb0[2], ra1[2], rb1[2];
@@ -432,14 +433,14 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
             __syncthreads();
             if (tid == 0) {
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t sbase = smem_u32(smem + stage * STAGE_BYTES);
+                // descriptors differ only in their 14-bit start-address field: one add per operand
+                const uint64_t d0 = desc_template + (uint64_t)(smem_u32(smem + stage * STAGE_BYTES) >> 4);
 #pragma unroll
                 for (int k8 = 0; k8 < TK / 8; ++k8) {
-                    const uint32_t koff = (uint32_t)(2 * k8 * LBO_BYTES);
-                    const uint64_t a_hi = make_desc(sbase + koff);
-                    const uint64_t a_lo = make_desc(sbase + OPERAND_BYTES + koff);
-                    const uint64_t b_hi = make_desc(sbase + 2 * OPERAND_BYTES + koff);
-                    const uint64_t b_lo = make_desc(sbase + 3 * OPERAND_BYTES + koff);
+                    const uint64_t a_hi = d0 + (uint64_t)((2 * k8 * LBO_BYTES) >> 4);
+                    const uint64_t a_lo = a_hi + (uint64_t)(OPERAND_BYTES >> 4);
+                    const uint64_t b_hi = a_hi + (uint64_t)((2 * OPERAND_BYTES) >> 4);
+                    const uint64_t b_lo = a_hi + (uint64_t)((3 * OPERAND_BYTES) >> 4);
                     const uint32_t acc = (kt > kt_beg || k8 > 0) ? 1u : 0u;
                     mma_tf32(tmem_d + 128, a_lo, b_hi, idesc, acc);   // cross terms: own accumulator
                     mma_tf32(tmem_d + 128, a_hi, b_lo, idesc, 1u);
