@@ -44,10 +44,18 @@ class GraphCSR:
         self.seg_offsets = torch.zeros(self.batch_size + 1, dtype=torch.int32, device=dev)
         self.seg_offsets[1:] = torch.cumsum(bnn, 0).to(torch.int32)
         self.node_seg = torch.repeat_interleave(
-            torch.arange(self.batch_size, device=dev, dtype=torch.int32), bnn
+            torch.arange(self.batch_size, device=dev, dtype=torch.int32), bnn, output_size=n
         ).contiguous()
         self.num_nodes = n
-        self.has_zero_in_degree = bool((in_deg == 0).any().item()) if n else False
+        self._in_deg = in_deg
+        self._has_zero_in_degree = None
+
+    @property
+    def has_zero_in_degree(self):
+        """Evaluated on demand (one device->host read): only GraphConv(allow_zero_in_degree=False) asks."""
+        if self._has_zero_in_degree is None:
+            self._has_zero_in_degree = bool((self._in_deg == 0).any().item()) if self.num_nodes else False
+        return self._has_zero_in_degree
 
     def scales(self, norm):
         if norm == "both":

@@ -94,7 +94,7 @@ class Net(BaseNet):
         with torch.no_grad():
             h_last = self.representation(self.g_last)
             post = ops.ExactGPPosterior(h_last, self.y_last, reg.kernel.scale, reg.kernel.variance, reg.log_sigma,
-                                        kind=reg._kind(), check=reg.check_positive_definite)
+                                        kind=reg._kind(), check=bool(reg.check_positive_definite))
             nb = g.batch_size
             means, variances = [], []
             for lo in range(0, nb, chunk_molecules):

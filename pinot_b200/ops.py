@@ -280,6 +280,7 @@ class _ExactGPLoss(torch.autograd.Function):
         ctx.save_for_backward(x, sc, var, ls, diag, e)
         ctx.cfg = (kind, int(exact_logdet), n, ld, scale.shape, variance.shape, log_sigma.shape, y.shape)
         ctx.info = info
+        _ExactGPLoss.last_info = info
         nll = out3[1] if exact_logdet else out3[0]
         return nll.reshape(1, 1)
 
@@ -309,8 +310,11 @@ class _ExactGPLoss(torch.autograd.Function):
         return dx, dy, dscale, dvar, dls, None, None, None
 
 
-def exact_gp_loss(x, y, scale, variance, log_sigma, kind="rbf", exact_logdet=False, check=True):
-    return _ExactGPLoss.apply(x, y, scale, variance, log_sigma, kind, bool(exact_logdet), bool(check))
+def exact_gp_loss(x, y, scale, variance, log_sigma, kind="rbf", exact_logdet=False, check=True, return_info=False):
+    """Exact-GP objective, shape (1, 1).  ``check=False`` leaves the factorisation status (LAPACK-style
+    ``info``) on the device; with ``return_info`` it is returned for a later ``check_info``."""
+    loss = _ExactGPLoss.apply(x, y, scale, variance, log_sigma, kind, bool(exact_logdet), bool(check))
+    return (loss, _ExactGPLoss.last_info) if return_info else loss
 
 
 @torch.no_grad()

@@ -59,8 +59,12 @@ class ExactGaussianProcessRegressor(GaussianProcessRegressor):
         self.log_sigma = torch.nn.Parameter(torch.tensor(log_sigma))
         assert logdet in ("trace", "exact")
         self.logdet = logdet
-        #: raise RuntimeError on a non-positive-definite kernel matrix (needs one device->host read)
+        #: True: raise RuntimeError on a non-positive-definite kernel matrix right away, like
+        #: torch.cholesky (one device->host read in the middle of the step); "deferred": keep the
+        #: factorisation status on the device and raise from verify(), which the caller runs where it
+        #: synchronises anyway (after reading the loss); False: never check.
         self.check_positive_definite = True
+        self._last_info = None
 
     def _kind(self):
         kind = getattr(self.kernel, "kind", None)
@@ -92,17 +96,25 @@ class ExactGaussianProcessRegressor(GaussianProcessRegressor):
         """Negative log likelihood, shape (1, 1) (:123-166)."""
         self._x_tr = x_tr
         self._y_tr = y_tr
-        return ops.exact_gp_loss(
+        immediate = self.check_positive_definite is True
+        loss, self._last_info = ops.exact_gp_loss(
             x_tr, y_tr, self.kernel.scale, self.kernel.variance, self.log_sigma, kind=self._kind(),
-            exact_logdet=(self.logdet == "exact"), check=self.check_positive_definite)
+            exact_logdet=(self.logdet == "exact"), check=immediate, return_info=True)
+        return loss
+
+    def verify(self):
+        """Raise RuntimeError if the last ``loss`` factorisation met a non-positive pivot (for
+        ``check_positive_definite="deferred"``).  Reads one int from the device."""
+        if self._last_info is not None and self.check_positive_definite:
+            ops.check_info(self._last_info)
 
     def condition(self, x_te, *args, x_tr=None, y_tr=None, **kwargs):
         """Predictive distribution ``MultivariateNormal(mean, cov)`` (:168-233).  Evaluated without
         autograd history (acquisition functions and metrics only consume values)."""
         mean, cov = ops.exact_gp_posterior(
             x_te, x_tr, y_tr, self.kernel.scale, self.kernel.variance, self.log_sigma, kind=self._kind(),
-            full_cov=True, check=self.check_positive_definite)
-        return _mvn_from_cov(mean, cov, check=self.check_positive_definite)
+            full_cov=True, check=bool(self.check_positive_definite))
+        return _mvn_from_cov(mean, cov, check=bool(self.check_positive_definite))
 
     def condition_marginal(self, x_te, x_tr=None, y_tr=None):
         """Predictive marginals ``Normal(mean, sqrt(var))`` without materialising the n_te x n_te
@@ -111,7 +123,7 @@ class ExactGaussianProcessRegressor(GaussianProcessRegressor):
         Not in the reference API."""
         mean, var = ops.exact_gp_posterior(
             x_te, x_tr, y_tr, self.kernel.scale, self.kernel.variance, self.log_sigma, kind=self._kind(),
-            full_cov=False, check=self.check_positive_definite)
+            full_cov=False, check=bool(self.check_positive_definite))
         return torch.distributions.normal.Normal(loc=mean, scale=var.clamp_min(0).sqrt(), validate_args=False)
 
 

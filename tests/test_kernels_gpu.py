@@ -344,3 +344,25 @@ def test_exact_gp_posterior(kind, n, nte, d):
     mean2, v = ops.exact_gp_posterior(*args, kind=kind, full_cov=False)
     assert rel_err(mean2, mean_w) < 1e-4
     assert max_rel_err(v, torch.diagonal(cov_w), floor=1e-3) < 1e-3
+
+
+def test_deferred_positive_definite_check():
+    """check_positive_definite="deferred": loss() does not synchronise; verify() raises afterwards."""
+    torch.manual_seed(0)
+    reg = pb.regressors.ExactGaussianProcessRegressor(8).to(DEV)
+    x = torch.randn(40, 8, device=DEV)
+    x[1] = x[0]                                   # duplicate points ...
+    with torch.no_grad():
+        reg.log_sigma.fill_(-40.0)                # ... and no noise: singular up to the 1e-5 jitter
+        reg.kernel.variance.fill_(12.0)           # amplitude e^12 swamps the jitter in fp32
+    y = torch.randn(40, 1, device=DEV)
+    reg.check_positive_definite = True
+    with pytest.raises(RuntimeError, match="not positive-definite"):
+        reg.loss(x, y)
+    reg.check_positive_definite = "deferred"
+    reg.loss(x, y)                                # no exception here
+    with pytest.raises(RuntimeError, match="not positive-definite"):
+        reg.verify()
+    reg.check_positive_definite = False
+    reg.loss(x, y)
+    reg.verify()                                  # checking switched off
