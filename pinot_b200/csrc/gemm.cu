@@ -303,13 +303,50 @@ int gemm(const GemmParams& g, cudaStream_t stream) {
 
 namespace {
 
-// dz = dy * act'(y) (tanh: 1 - y^2), written in place or to dz, plus db[n] += sum_m dz[m, n].
+// dz = dy * act'(y) (tanh: 1 - y^2), written to dz, plus db[n] += sum_m dz[m, n].
+// Thread = 4 consecutive columns (16-byte accesses) of `rows_per_block` rows; column sums leave the
+// block as one atomic per column.  N % 4 == 0 and 16-byte aligned pointers (vec) or the scalar path.
 __global__ void __launch_bounds__(256)
 act_bwd_bias_kernel(const float* __restrict__ dy, const float* __restrict__ y, float* __restrict__ dz,
-                    float* __restrict__ db, int64_t M, int N, int act, int rows_per_block) {
-    // blockDim = (min(N,256) rounded to 32..., ) one thread per column, loop over a row chunk.
+                    float* __restrict__ db, int64_t M, int N, int act, int rows_per_block, int vec) {
     const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
     const int64_t r1 = min(M, r0 + rows_per_block);
+    if (vec) {
+        const int nv = N >> 2;                       // float4 columns
+        const int cpr = min(nv, (int)blockDim.x);     // threads along a row
+        const int tr = threadIdx.x / cpr, tc = threadIdx.x - tr * cpr;
+        const int row_step = blockDim.x / cpr;
+        const bool active = tr < row_step;   // leftover threads when cpr does not divide the block
+        for (int c = tc + blockIdx.y * cpr; c < nv; c += cpr * gridDim.y) {
+            float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int64_t r = r0 + tr; active && r < r1; r += row_step) {
+                float4 g = __ldg(reinterpret_cast<const float4*>(dy + r * N) + c);
+                if (act == 1) {
+                    const float4 t = __ldg(reinterpret_cast<const float4*>(y + r * N) + c);
+                    g.x *= (1.f - t.x * t.x); g.y *= (1.f - t.y * t.y);
+                    g.z *= (1.f - t.z * t.z); g.w *= (1.f - t.w * t.w);
+                }
+                if (dz) reinterpret_cast<float4*>(dz + r * N)[c] = g;
+                s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
+            }
+            if (db) {
+                // combine the row lanes of this block in shared memory: one atomic per column
+                __shared__ float4 part[256];
+                part[threadIdx.x] = s;
+                __syncthreads();
+                if (tr == 0 && active) {
+                    for (int k = 1; k < row_step; ++k) {
+                        const float4 o = part[k * cpr + tc];
+                        s.x += o.x; s.y += o.y; s.z += o.z; s.w += o.w;
+                    }
+                    atomicAdd(db + 4 * c + 0, s.x); atomicAdd(db + 4 * c + 1, s.y);
+                    atomicAdd(db + 4 * c + 2, s.z); atomicAdd(db + 4 * c + 3, s.w);
+                }
+                __syncthreads();
+            }
+        }
+        return;
+    }
     for (int n = threadIdx.x + blockIdx.y * blockDim.x; n < N; n += blockDim.x * gridDim.y) {
         float s = 0.f;
         for (int64_t r = r0; r < r1; ++r) {
@@ -343,7 +380,7 @@ int pinot_b200_sgemm(int transA, int transB, int64_t M, int64_t N, int64_t K, fl
     // Short-and-wide products (weight gradients) get split-K so that all SMs participate.
     const int64_t tiles = pb::ceil_div(M, 128) * pb::ceil_div(N, 128);
     if ((beta == 0.f || beta == 1.f) && tiles < 148 && K >= 2048) {
-        int64_t s = 296 / tiles;
+        int64_t s = 296 / tiles;   // two CTAs per SM
         const int64_t ktiles = pb::ceil_div(K, 16);
         if (s > ktiles / 8) s = ktiles / 8;
         if (s > 1) g.splitk = (int)s;
@@ -384,11 +421,20 @@ int pinot_b200_node_update_bwd(const float* dy, const float* y, const float* x, 
     const float* dz = dy;
     if (act == 1 || db) {
         if (db) PB_CUDA(cudaMemsetAsync(db, 0, sizeof(float) * out_feats, stream));
-        const int rows_per_block = 64;
-        const int tx = (int)(out_feats >= 256 ? 256 : ((out_feats + 31) / 32) * 32);
-        dim3 grid((unsigned)pb::ceil_div(n_rows, rows_per_block), (unsigned)pb::ceil_div(out_feats, tx));
-        pb::act_bwd_bias_kernel<<<grid, tx, 0, stream>>>(dy, y, act == 1 ? dz_scratch : nullptr, db,
-                                                         n_rows, (int)out_feats, act, rows_per_block);
+        const int vec = (out_feats % 4 == 0) && pb::aligned16(dy) && (!y || pb::aligned16(y)) &&
+                        (act != 1 || pb::aligned16(dz_scratch));
+        if (vec) {
+            const int rows_per_block = 128;
+            dim3 grid((unsigned)pb::ceil_div(n_rows, rows_per_block), (unsigned)pb::ceil_div(out_feats / 4, 256));
+            pb::act_bwd_bias_kernel<<<grid, 256, 0, stream>>>(dy, y, act == 1 ? dz_scratch : nullptr, db, n_rows,
+                                                             (int)out_feats, act, rows_per_block, 1);
+        } else {
+            const int rows_per_block = 64;
+            const int tx = (int)(out_feats >= 256 ? 256 : ((out_feats + 31) / 32) * 32);
+            dim3 grid((unsigned)pb::ceil_div(n_rows, rows_per_block), (unsigned)pb::ceil_div(out_feats, tx));
+            pb::act_bwd_bias_kernel<<<grid, tx, 0, stream>>>(dy, y, act == 1 ? dz_scratch : nullptr, db, n_rows,
+                                                            (int)out_feats, act, rows_per_block, 0);
+        }
         int rc = pb::check_launch("node_update_bwd/act_bwd_bias");
         if (rc) return rc;
         if (act == 1) dz = dz_scratch;

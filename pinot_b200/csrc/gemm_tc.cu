@@ -296,6 +296,11 @@ __device__ __forceinline__ void epilogue_rows(const KParams& p, const float* til
             const float4 acc = *reinterpret_cast<const float4*>(tile + rl * EPI_LD + c4);
             const float a4[4] = {acc.x, acc.y, acc.z, acc.w};
             float* cp = p.C + (int64_t)m * p.ldc + n;
+            if (p.splitk > 1 && p.vecC && n + 3 < p.N && (!p.lower || n + 3 <= m)) {
+                // split-K partial sums: one 16-byte vector reduction instead of four scalar atomics
+                atomicAdd(reinterpret_cast<float4*>(cp), make_float4(alpha * a4[0], alpha * a4[1], alpha * a4[2], alpha * a4[3]));
+                continue;
+            }
             const float um = (last_chunk && p.r1u) ? __ldg(p.r1u + m) * r1c : 0.f;
 #pragma unroll 1
             for (int j = 0; j < 4; ++j) {
