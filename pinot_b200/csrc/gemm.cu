@@ -317,9 +317,11 @@ act_bwd_bias_kernel(const float* __restrict__ dy, const float* __restrict__ y, f
         const int tr = threadIdx.x / cpr, tc = threadIdx.x - tr * cpr;
         const int row_step = blockDim.x / cpr;
         const bool active = tr < row_step;   // leftover threads when cpr does not divide the block
-        for (int c = tc + blockIdx.y * cpr; c < nv; c += cpr * gridDim.y) {
+        for (int cbase = blockIdx.y * cpr; cbase < nv; cbase += cpr * gridDim.y) {   // uniform trip count
+            const int c = cbase + tc;
+            const bool valid = active && c < nv;
             float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-            for (int64_t r = r0 + tr; active && r < r1; r += row_step) {
+            for (int64_t r = r0 + tr; valid && r < r1; r += row_step) {
                 float4 g = __ldg(reinterpret_cast<const float4*>(dy + r * N) + c);
                 if (act == 1) {
                     const float4 t = __ldg(reinterpret_cast<const float4*>(y + r * N) + c);
@@ -334,7 +336,7 @@ act_bwd_bias_kernel(const float* __restrict__ dy, const float* __restrict__ y, f
                 __shared__ float4 part[256];
                 part[threadIdx.x] = s;
                 __syncthreads();
-                if (tr == 0 && active) {
+                if (tr == 0 && valid) {
                     for (int k = 1; k < row_step; ++k) {
                         const float4 o = part[k * cpr + tc];
                         s.x += o.x; s.y += o.y; s.z += o.z; s.w += o.w;
