@@ -22,6 +22,7 @@
 //     epilogue as the FFMA kernel (alpha/beta, bias, tanh, rank-1 term, lower/mirror masks,
 //     split-K atomics, Cholesky look-ahead).
 #include "gemm_params.cuh"
+#include <stdlib.h>
 
 namespace pb {
 
@@ -37,20 +38,28 @@ namespace pb {
 
 namespace {
 
-constexpr int TM = 128, TN = 128, TK = 16;     // CTA tile; TK fp32 columns per pipeline stage
+constexpr int TM = 128, TK = 16;               // CTA tile rows; TK fp32 columns per pipeline stage
 constexpr int STAGES = 3;
 constexpr int NTHREADS = 256;
 constexpr int SBO_BYTES = 128;                 // between 8-row groups
-constexpr int LBO_BYTES = (TM / 8) * 128 + 32; // between K-adjacent core matrices (+32 B pad)
 constexpr int KC_PER_STAGE = TK / 4;           // 16-byte K chunks per stage
-constexpr int OPERAND_BYTES = KC_PER_STAGE * LBO_BYTES;          // one of A_hi, A_lo, B_hi, B_lo
-constexpr int STAGE_BYTES = 4 * OPERAND_BYTES;
-constexpr int PIPE_BYTES = STAGES * STAGE_BYTES;
-constexpr int DIAG_BYTES = (DIAG_SMEM_FLOATS > SOLVE_SMEM_FLOATS ? DIAG_SMEM_FLOATS : SOLVE_SMEM_FLOATS) * 4;
-constexpr int DYN_SMEM_BYTES = (PIPE_BYTES > DIAG_BYTES ? PIPE_BYTES : DIAG_BYTES) + 128;
 constexpr int EPI_LD = 36;                     // floats per row of a warp's 32x32 epilogue staging tile
-constexpr int TMEM_COLS = 256;                // [0,128): hi.hi accumulator, [128,256): cross terms
-constexpr int KCHUNK = 512;                   // accumulator is flushed to C every KCHUNK columns
+constexpr int KCHUNK = 512;                    // accumulator is flushed to C every KCHUNK columns
+constexpr int DIAG_BYTES = (DIAG_SMEM_FLOATS > SOLVE_SMEM_FLOATS ? DIAG_SMEM_FLOATS : SOLVE_SMEM_FLOATS) * 4;
+
+// Geometry of a CTA tile of 128 x BN outputs (BN = 128: two CTAs per SM; BN = 256: one CTA per SM, all
+// 512 TMEM columns, half the shared-memory operand traffic per flop -- for large products).
+template <int BN>
+struct Geo {
+    static constexpr int LBO_A = (TM / 8) * 128 + 32;   // between K-adjacent core matrices (+32 B pad)
+    static constexpr int LBO_B = (BN / 8) * 128 + 32;
+    static constexpr int OP_A = KC_PER_STAGE * LBO_A;    // one of A_hi, A_lo
+    static constexpr int OP_B = KC_PER_STAGE * LBO_B;    // one of B_hi, B_lo
+    static constexpr int STAGE = 2 * OP_A + 2 * OP_B;
+    static constexpr int PIPE = STAGES * STAGE;
+    static constexpr int DYN_SMEM = (PIPE > DIAG_BYTES ? PIPE : DIAG_BYTES) + 128;
+    static constexpr int TMEM_COLS = 2 * BN;             // [0,BN): hi.hi accumulator, [BN,2BN): cross terms
+};
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -72,10 +81,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 }
 
 // 64-bit shared-memory matrix descriptor: K-major, SWIZZLE_NONE, version 1 (sm_100).
-__device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, int lbo_bytes) {
     uint64_t d = 0;
     d |= (uint64_t)((saddr >> 4) & 0x3FFF);                    // start address      bits [0,14)
-    d |= (uint64_t)((LBO_BYTES >> 4) & 0x3FFF) << 16;          // leading byte off.  bits [16,30)
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;          // leading byte off.  bits [16,30)
     d |= (uint64_t)((SBO_BYTES >> 4) & 0x3FFF) << 32;          // stride byte off.   bits [32,46)
     d |= (uint64_t)1 << 46;                                    // descriptor version bits [46,48)
     return d;                                                  // layout type 0 = no swizzle
@@ -110,16 +119,20 @@ __device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
 }
 
 // ---- operand staging -------------------------------------------------------------------------
-// Register image of one K-slab of one operand: 2 x float4 per thread.
+// Register image of one K-slab of an operand tile of 128 * H rows (H = 1 or 2): 2 * H float4 per
+// thread.  The two layouts below are applied to each 128-row half in turn (images [2h], [2h+1]).
 //   k-contiguous storage ([row][k]):   thread -> row = tid/4 + 64*i, kc = tid%4   (float4 along k)
-//   row-contiguous storage ([k][row]): thread -> k = tid/32 + 8*i, rows (tid%32)*4 .. +3
+//   row-contiguous storage ([k][row]): thread -> kc = tid/64, row pair rp = tid%64; four float2
+//     loads (k = 4 kc + i, rows 2 rp, 2 rp + 1) are transposed in registers into one float4 per
+//     row, so the shared-memory stores stay 16-byte vectors along k.
+template <int H>
 __device__ __forceinline__ void tc_load_kcontig(const float* __restrict__ P, int64_t ld, int rows, int kend,
                                                 int row0, int k0, int vec, const float* __restrict__ kscale,
-                                                float4 (&r)[2]) {
+                                                float4 (&r)[2 * H]) {
     const int tid = threadIdx.x;
     const int k = k0 + (tid & 3) * 4;
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < 2 * H; ++i) {
         const int row = row0 + (tid >> 2) + 64 * i;
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
         if (row < rows && k < kend) {
@@ -142,68 +155,71 @@ __device__ __forceinline__ void tc_load_kcontig(const float* __restrict__ P, int
         r[i] = v;
     }
 }
-__device__ __forceinline__ void tc_store_kcontig(uint8_t* hi, uint8_t* lo, const float4 (&r)[2]) {
+template <int H>
+__device__ __forceinline__ void tc_store_kcontig(uint8_t* hi, uint8_t* lo, int lbo, const float4 (&r)[2 * H]) {
     const int tid = threadIdx.x;
     const int kc = tid & 3;
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < 2 * H; ++i) {
         const int row = (tid >> 2) + 64 * i;
         float4 h, l;
         split_tf32(r[i].x, h.x, l.x);
         split_tf32(r[i].y, h.y, l.y);
         split_tf32(r[i].z, h.z, l.z);
         split_tf32(r[i].w, h.w, l.w);
-        const int off = kc * LBO_BYTES + row * 16;   // (row/8)*128 + (row%8)*16 == row*16
+        const int off = kc * lbo + row * 16;   // (row/8)*128 + (row%8)*16 == row*16
         *reinterpret_cast<float4*>(hi + off) = h;
         *reinterpret_cast<float4*>(lo + off) = l;
     }
 }
 
-// row-contiguous storage ([k][row]): thread -> kc = tid/64, row pair rp = tid%64; four float2 loads
-// (k = 4 kc + i, rows 2 rp, 2 rp + 1) are transposed in registers into one float4 per row, so the
-// shared-memory stores stay 16-byte vectors along k.  r[0] = row 2rp, r[1] = row 2rp + 1.
+template <int H>
 __device__ __forceinline__ void tc_load_rowcontig(const float* __restrict__ P, int64_t ld, int rows, int kend,
                                                   int row0, int k0, int vec, const float* __restrict__ kscale,
-                                                  float4 (&r)[2]) {
+                                                  float4 (&r)[2 * H]) {
     const int tid = threadIdx.x;
-    const int row = row0 + (tid & 63) * 2;
     const int kbase = k0 + (tid >> 6) * 4;
-    float a[4], b[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int k = kbase + i;
-        float x = 0.f, y = 0.f;
-        if (k < kend && row < rows) {
-            const float* src = P + (int64_t)k * ld + row;
-            if (vec && row + 1 < rows) {
-                const float2 t = __ldg(reinterpret_cast<const float2*>(src));
-                x = t.x; y = t.y;
-            } else {
-                x = __ldg(src);
-                if (row + 1 < rows) y = __ldg(src + 1);
+    for (int h = 0; h < H; ++h) {
+        const int row = row0 + 128 * h + (tid & 63) * 2;
+        float a[4], b[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int k = kbase + i;
+            float x = 0.f, y = 0.f;
+            if (k < kend && row < rows) {
+                const float* src = P + (int64_t)k * ld + row;
+                if (vec && row + 1 < rows) {
+                    const float2 t = __ldg(reinterpret_cast<const float2*>(src));
+                    x = t.x; y = t.y;
+                } else {
+                    x = __ldg(src);
+                    if (row + 1 < rows) y = __ldg(src + 1);
+                }
+                if (kscale) {
+                    const float s = __ldg(kscale + k);
+                    x *= s; y *= s;
+                }
             }
-            if (kscale) {
-                const float s = __ldg(kscale + k);
-                x *= s; y *= s;
-            }
+            a[i] = x; b[i] = y;
         }
-        a[i] = x; b[i] = y;
+        r[2 * h] = make_float4(a[0], a[1], a[2], a[3]);
+        r[2 * h + 1] = make_float4(b[0], b[1], b[2], b[3]);
     }
-    r[0] = make_float4(a[0], a[1], a[2], a[3]);
-    r[1] = make_float4(b[0], b[1], b[2], b[3]);
 }
-__device__ __forceinline__ void tc_store_rowcontig(uint8_t* hi, uint8_t* lo, const float4 (&r)[2]) {
+template <int H>
+__device__ __forceinline__ void tc_store_rowcontig(uint8_t* hi, uint8_t* lo, int lbo, const float4 (&r)[2 * H]) {
     const int tid = threadIdx.x;
     const int kc = tid >> 6;
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
-        const int row = (tid & 63) * 2 + i;
+    for (int i = 0; i < 2 * H; ++i) {
+        const int row = 128 * (i >> 1) + (tid & 63) * 2 + (i & 1);
         float4 h, l;
         split_tf32(r[i].x, h.x, l.x);
         split_tf32(r[i].y, h.y, l.y);
         split_tf32(r[i].z, h.z, l.z);
         split_tf32(r[i].w, h.w, l.w);
-        const int off = kc * LBO_BYTES + row * 16;
+        const int off = kc * lbo + row * 16;
         *reinterpret_cast<float4*>(hi + off) = h;
         *reinterpret_cast<float4*>(lo + off) = l;
     }
@@ -323,13 +339,15 @@ __device__ __forceinline__ void epilogue_rows(const KParams& p, const float* til
     }
 }
 
-template <bool TA, bool TB, int EPI, bool POST>
-__global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
+template <bool TA, bool TB, int EPI, bool POST, int BN>
+__global__ void __launch_bounds__(NTHREADS, BN == 128 ? 2 : 1) tgemm_kernel(const KParams p) {
+    using G = Geo<BN>;
+    constexpr int HB = BN / 128;
     extern __shared__ __align__(128) uint8_t dyn_smem[];
     __shared__ __align__(8) uint64_t mma_bar[STAGES];
     __shared__ uint32_t tmem_base_holder;
 
-    const int m0 = blockIdx.y * TM, n0 = blockIdx.x * TN;
+    const int m0 = blockIdx.y * TM, n0 = blockIdx.x * BN;
     if (p.lower && n0 > m0 + TM - 1) return;
 
     int kb = 0, ke = p.K;
@@ -356,7 +374,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
     }
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_holder)),
-                     "r"((uint32_t)TMEM_COLS)
+                     "r"((uint32_t)G::TMEM_COLS)
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
@@ -367,38 +385,39 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
     PB_STAMP(1);
 
     // MMA N: the valid columns of this tile rounded up to a legal UMMA N (multiple of 16)
-    const int n_valid = min(TN, p.N - n0);
-    const int n_mma = min(TN, ((n_valid + 15) / 16) * 16);
+    const int n_valid = min(BN, p.N - n0);
+    const int n_mma = min(BN, ((n_valid + 15) / 16) * 16);
     const uint32_t idesc = make_idesc(n_mma);
-    const uint64_t desc_template = make_desc(0);
+    const uint64_t desc_a = make_desc(0, G::LBO_A), desc_b = make_desc(0, G::LBO_B);
 
     // two register images per operand: two K-slabs are in flight while a third is being split
-    float4 ra0[2], rb0[2], ra1[2], rb1[2];
+    float4 ra0[2], rb0[2 * HB], ra1[2], rb1[2 * HB];
     auto gload0 = [&](int k0) {
-        if (TA) tc_load_rowcontig(p.A, p.lda, p.M, ke, m0, k0, p.vecA, p.kscale, ra0);
-        else    tc_load_kcontig(p.A, p.lda, p.M, ke, m0, k0, p.vecA, p.kscale, ra0);
-        if (TB) tc_load_kcontig(p.B, p.ldb, p.N, ke, n0, k0, p.vecB, nullptr, rb0);
-        else    tc_load_rowcontig(p.B, p.ldb, p.N, ke, n0, k0, p.vecB, nullptr, rb0);
+        if (TA) tc_load_rowcontig<1>(p.A, p.lda, p.M, ke, m0, k0, p.vecA, p.kscale, ra0);
+        else    tc_load_kcontig<1>(p.A, p.lda, p.M, ke, m0, k0, p.vecA, p.kscale, ra0);
+        if (TB) tc_load_kcontig<HB>(p.B, p.ldb, p.N, ke, n0, k0, p.vecB, nullptr, rb0);
+        else    tc_load_rowcontig<HB>(p.B, p.ldb, p.N, ke, n0, k0, p.vecB, nullptr, rb0);
     };
     auto gload1 = [&](int k0) {
-        if (TA) tc_load_rowcontig(p.A, p.lda, p.M, ke, m0, k0, p.vecA, p.kscale, ra1);
-        else    tc_load_kcontig(p.A, p.lda, p.M, ke, m0, k0, p.vecA, p.kscale, ra1);
-        if (TB) tc_load_kcontig(p.B, p.ldb, p.N, ke, n0, k0, p.vecB, nullptr, rb1);
-        else    tc_load_rowcontig(p.B, p.ldb, p.N, ke, n0, k0, p.vecB, nullptr, rb1);
+        if (TA) tc_load_rowcontig<1>(p.A, p.lda, p.M, ke, m0, k0, p.vecA, p.kscale, ra1);
+        else    tc_load_kcontig<1>(p.A, p.lda, p.M, ke, m0, k0, p.vecA, p.kscale, ra1);
+        if (TB) tc_load_kcontig<HB>(p.B, p.ldb, p.N, ke, n0, k0, p.vecB, nullptr, rb1);
+        else    tc_load_rowcontig<HB>(p.B, p.ldb, p.N, ke, n0, k0, p.vecB, nullptr, rb1);
     };
+    // stage layout: A_hi | A_lo | B_hi | B_lo
     auto sstore0 = [&](int stage) {
-        uint8_t* base = smem + stage * STAGE_BYTES;
-        if (TA) tc_store_rowcontig(base, base + OPERAND_BYTES, ra0);
-        else    tc_store_kcontig(base, base + OPERAND_BYTES, ra0);
-        if (TB) tc_store_kcontig(base + 2 * OPERAND_BYTES, base + 3 * OPERAND_BYTES, rb0);
-        else    tc_store_rowcontig(base + 2 * OPERAND_BYTES, base + 3 * OPERAND_BYTES, rb0);
+        uint8_t* base = smem + stage * G::STAGE;
+        if (TA) tc_store_rowcontig<1>(base, base + G::OP_A, G::LBO_A, ra0);
+        else    tc_store_kcontig<1>(base, base + G::OP_A, G::LBO_A, ra0);
+        if (TB) tc_store_kcontig<HB>(base + 2 * G::OP_A, base + 2 * G::OP_A + G::OP_B, G::LBO_B, rb0);
+        else    tc_store_rowcontig<HB>(base + 2 * G::OP_A, base + 2 * G::OP_A + G::OP_B, G::LBO_B, rb0);
     };
     auto sstore1 = [&](int stage) {
-        uint8_t* base = smem + stage * STAGE_BYTES;
-        if (TA) tc_store_rowcontig(base, base + OPERAND_BYTES, ra1);
-        else    tc_store_kcontig(base, base + OPERAND_BYTES, ra1);
-        if (TB) tc_store_kcontig(base + 2 * OPERAND_BYTES, base + 3 * OPERAND_BYTES, rb1);
-        else    tc_store_rowcontig(base + 2 * OPERAND_BYTES, base + 3 * OPERAND_BYTES, rb1);
+        uint8_t* base = smem + stage * G::STAGE;
+        if (TA) tc_store_rowcontig<1>(base, base + G::OP_A, G::LBO_A, ra1);
+        else    tc_store_kcontig<1>(base, base + G::OP_A, G::LBO_A, ra1);
+        if (TB) tc_store_kcontig<HB>(base + 2 * G::OP_A, base + 2 * G::OP_A + G::OP_B, G::LBO_B, rb1);
+        else    tc_store_rowcontig<HB>(base + 2 * G::OP_A, base + 2 * G::OP_A + G::OP_B, G::LBO_B, rb1);
     };
 
     // epilogue constants
@@ -409,7 +428,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
         r1c *= s;
     }
     const int q = warp & 3;                  // TMEM lane quadrant of this warp
-    const int col_half = (warp >> 2) * 64;   // warps 0-3: columns 0..63, warps 4-7: 64..127
+    const int col_half = (warp >> 2) * (BN / 2);   // warps 0-3: left half of the columns, warps 4-7: right half
 
     const int tiles_per_chunk = KCHUNK / TK;
     const int num_chunks = num_k > 0 ? (num_k + tiles_per_chunk - 1) / tiles_per_chunk : 1;
@@ -439,16 +458,16 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
             if (tid == 0) {
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 // descriptors differ only in their 14-bit start-address field: one add per operand
-                const uint64_t d0 = desc_template + (uint64_t)(smem_u32(smem + stage * STAGE_BYTES) >> 4);
+                const uint32_t s16 = smem_u32(smem + stage * G::STAGE) >> 4;
 #pragma unroll
                 for (int k8 = 0; k8 < TK / 8; ++k8) {
-                    const uint64_t a_hi = d0 + (uint64_t)((2 * k8 * LBO_BYTES) >> 4);
-                    const uint64_t a_lo = a_hi + (uint64_t)(OPERAND_BYTES >> 4);
-                    const uint64_t b_hi = a_hi + (uint64_t)((2 * OPERAND_BYTES) >> 4);
-                    const uint64_t b_lo = a_hi + (uint64_t)((3 * OPERAND_BYTES) >> 4);
+                    const uint64_t a_hi = desc_a + (uint64_t)(s16 + ((2 * k8 * G::LBO_A) >> 4));
+                    const uint64_t a_lo = a_hi + (uint64_t)(G::OP_A >> 4);
+                    const uint64_t b_hi = desc_b + (uint64_t)(s16 + ((2 * G::OP_A + 2 * k8 * G::LBO_B) >> 4));
+                    const uint64_t b_lo = b_hi + (uint64_t)(G::OP_B >> 4);
                     const uint32_t acc = (kt > kt_beg || k8 > 0) ? 1u : 0u;
-                    mma_tf32(tmem_d + 128, a_lo, b_hi, idesc, acc);   // cross terms: own accumulator
-                    mma_tf32(tmem_d + 128, a_hi, b_lo, idesc, 1u);
+                    mma_tf32(tmem_d + BN, a_lo, b_hi, idesc, acc);   // cross terms: own accumulator
+                    mma_tf32(tmem_d + BN, a_hi, b_lo, idesc, 1u);
                     mma_tf32(tmem_d, a_hi, b_hi, idesc, acc);
                 }
                 mma_commit(&mma_bar[stage]);
@@ -466,7 +485,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
         // belong to the last chunk only.
         const float beta = first_chunk ? p.beta : 1.f;
 #pragma unroll 1
-        for (int cc = 0; cc < 64; cc += 32) {
+        for (int cc = 0; cc < BN / 2; cc += 32) {
             const int c0 = col_half + cc;
             uint32_t v[32], w[32];
             if (num_k > 0 && c0 < n_mma) {
@@ -489,7 +508,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
                       "=r"(w[8]), "=r"(w[9]), "=r"(w[10]), "=r"(w[11]), "=r"(w[12]), "=r"(w[13]), "=r"(w[14]), "=r"(w[15]),
                       "=r"(w[16]), "=r"(w[17]), "=r"(w[18]), "=r"(w[19]), "=r"(w[20]), "=r"(w[21]), "=r"(w[22]), "=r"(w[23]),
                       "=r"(w[24]), "=r"(w[25]), "=r"(w[26]), "=r"(w[27]), "=r"(w[28]), "=r"(w[29]), "=r"(w[30]), "=r"(w[31])
-                    : "r"(taddr + 128u)
+                    : "r"(taddr + (uint32_t)BN)
                     : "memory");
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                 if (cc == 0) PB_STAMP(11);
@@ -514,7 +533,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
             epilogue_rows<EPI>(p, tile, alpha, beta, r1c, last_chunk, m0, n0, q, c0, lane);
             __syncwarp();
             if (cc == 0) PB_STAMP(13);
-            if (cc == 32) PB_STAMP(14);
+            if (cc == BN / 2 - 32) PB_STAMP(14);
         }
         // all warps have drained the accumulators before the next chunk overwrites them
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -525,7 +544,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) tgemm_kernel(const KParams p) {
     PB_STAMP(3);
     // ---- teardown: every warp is done reading TMEM (synchronised above) before warp 0 frees it ----
     if (warp == 0) {
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)TMEM_COLS)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)G::TMEM_COLS)
                      : "memory");
     }
 
@@ -561,21 +580,36 @@ extern "C" __attribute__((visibility("default"))) int pinot_b200_debug_times(uns
 #endif
 
 int launch_gemm_tc(const KParams& p, bool transA, bool transB, dim3 grid, cudaStream_t stream) {
-    auto launch = [&](auto kern) -> int {
-        PB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, DYN_SMEM_BYTES));
-        kern<<<grid, NTHREADS, DYN_SMEM_BYTES, stream>>>(p);
-        return check_launch("gemm (tcgen05)");
-    };
     // epilogue variant (see epilogue_rows): the generic one whenever a specialised one is not built
     int epi = 0;
     if (p.splitk > 1 || !p.vecC) epi = 3;
     else if (p.r1u || p.mirror) epi = (!transA && transB) ? 2 : 3;
     else if (p.act) epi = (!transA) ? 1 : 3;
+    // wide tiles (128 x 256, one CTA per SM) for large products: half the shared-memory operand
+    // traffic per flop; PINOT_B200_WIDE=0 switches them off
+    static const bool wide_ok = [] { const char* v = getenv("PINOT_B200_WIDE"); return !(v && v[0] == '0'); }();
+    const bool wide = wide_ok && !p.post_wdiag && p.splitk == 1 && (epi == 0 || epi == 2) && p.M >= 1024 &&
+                      p.N >= 1024 && p.K >= 256;
+    auto launch = [&](auto kern, int smem_bytes, dim3 g) -> int {
+        PB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+        kern<<<g, NTHREADS, smem_bytes, stream>>>(p);
+        return check_launch("gemm (tcgen05)");
+    };
+    if (wide) {
+        dim3 g2((unsigned)ceil_div(p.N, 256), grid.y, 1);
+#define PB_TCW(TA_, TB_, E_) return launch(tgemm_kernel<TA_, TB_, E_, false, 256>, Geo<256>::DYN_SMEM, g2)
+        if (epi == 2) PB_TCW(false, true, 2);
+        if (!transA && !transB) PB_TCW(false, false, 0);
+        if (!transA && transB) PB_TCW(false, true, 0);
+        if (transA && !transB) PB_TCW(true, false, 0);
+        PB_TCW(true, true, 0);
+#undef PB_TCW
+    }
     if (p.post_wdiag) {
         PB_REQUIRE(!transA && transB && epi == 0, "gemm: the Cholesky look-ahead is built for the NT update only");
-        return launch(tgemm_kernel<false, true, 0, true>);
+        return launch(tgemm_kernel<false, true, 0, true, 128>, Geo<128>::DYN_SMEM, grid);
     }
-#define PB_TC(TA_, TB_, E_) return launch(tgemm_kernel<TA_, TB_, E_, false>)
+#define PB_TC(TA_, TB_, E_) return launch(tgemm_kernel<TA_, TB_, E_, false, 128>, Geo<128>::DYN_SMEM, grid)
     if (!transA && !transB) { if (epi == 0) PB_TC(false, false, 0); if (epi == 1) PB_TC(false, false, 1); PB_TC(false, false, 3); }
     if (!transA && transB)  { if (epi == 0) PB_TC(false, true, 0);  if (epi == 1) PB_TC(false, true, 1);
                               if (epi == 2) PB_TC(false, true, 2);  PB_TC(false, true, 3); }

@@ -64,6 +64,21 @@ def main():
             b = torch.randn((n, k) if tb else (k, n), device=DEV)
             want = (a.double().t() if ta else a.double()) @ (b.double().t() if tb else b.double())
             report("rand ta=%d tb=%d m%d n%d k%d" % (ta, tb, m, n, k), sgemm(a, b, ta, tb, m, n, k), want)
+    # wide-tile path (M, N >= 1024, K >= 256): exact integers, odd shapes, all layouts
+    m, n, k = 1280, 1536, 256
+    a = ((torch.arange(m * k).reshape(m, k) * 7 + 3) % 11 - 5).float().to(DEV)
+    b = ((torch.arange(n * k).reshape(n, k) * 5 + 1) % 13 - 6).float().to(DEV)
+    report("wide int NT m%d n%d k%d" % (m, n, k), sgemm(a, b, False, True, m, n, k), a.double() @ b.double().t())
+    for ta in (False, True):
+        for tb in (False, True):
+            m, n, k = 1100, 1300, 300
+            a = torch.randn((k, m) if ta else (m, k), device=DEV)
+            b = torch.randn((n, k) if tb else (k, n), device=DEV)
+            want = (a.double().t() if ta else a.double()) @ (b.double().t() if tb else b.double())
+            report("wide rand ta=%d tb=%d m%d n%d k%d" % (ta, tb, m, n, k), sgemm(a, b, ta, tb, m, n, k), want)
+    a = torch.randn(2048, 1000, device=DEV); b = torch.randn(1000, 2048, device=DEV); c0 = torch.randn(2048, 2048, device=DEV)
+    report("wide alpha/beta NN k=1000", sgemm(a, b, False, False, 2048, 2048, 1000, alpha=-1.0, beta=1.0, c=c0.clone()),
+           c0.double() - a.double() @ b.double())
     # beta / accumulate
     a = torch.randn(300, 200, device=DEV)
     b = torch.randn(200, 150, device=DEV)
