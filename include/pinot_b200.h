@@ -99,6 +99,17 @@ PINOT_B200_API int pinot_b200_sgemm(int transA, int transB, int64_t M, int64_t N
                      const float* A, int64_t lda, const float* B, int64_t ldb, float beta, float* C,
                      int64_t ldc, cudaStream_t stream);
 
+/* C = alpha A B^T + beta C for LARGE products with A (M x K) and B (N x K) both row-major: the same
+ * 3xTF32 arithmetic as pinot_b200_sgemm(0, 1, ...), but the operands are split ONCE into hi / lo arrays
+ * in `workspace` and streamed into the tensor cores by TMA (cp.async.bulk.tensor) from a producer warp.
+ * Same reference call sites as pinot_b200_sgemm (the `@` products of
+ * pinot/regressors/gaussian_process_regressor.py:212,218,392-414).  All pointers 16-byte aligned,
+ * K and the leading dimensions multiples of 4; workspace_bytes >= ..._workspace_bytes(M, N, K). */
+PINOT_B200_API int64_t pinot_b200_sgemm_nt_tma_workspace_bytes(int64_t M, int64_t N, int64_t K);
+PINOT_B200_API int pinot_b200_sgemm_nt_tma(int64_t M, int64_t N, int64_t K, float alpha, const float* A, int64_t lda,
+                            const float* B, int64_t ldb, float beta, float* C, int64_t ldc, void* workspace,
+                            int64_t workspace_bytes, cudaStream_t stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Kernel (3): Gram matrix.  kind 0 = RBF (pinot/regressors/kernels/rbf.py:31-55: exp(variance) *
  * exp(-0.5 * ||(x - x') * exp(scale)||_2)), kind 1 = Matern-5/2 (pinot/regressors/kernels/matern.py:30-63).

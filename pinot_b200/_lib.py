@@ -30,6 +30,8 @@ SIGNATURES = {
     "pinot_b200_node_update_fwd": [_ptr, _ptr, _ptr, _ptr, _i64, _i64, _i64, _i32, _i32, _i32, _ptr],
     "pinot_b200_node_update_bwd": [_ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i64, _i64, _i32, _i32, _ptr],
     "pinot_b200_sgemm": [_i32, _i32, _i64, _i64, _i64, _f32, _ptr, _i64, _ptr, _i64, _f32, _ptr, _i64, _ptr],
+    "pinot_b200_sgemm_nt_tma_workspace_bytes": [_i64, _i64, _i64],
+    "pinot_b200_sgemm_nt_tma": [_i64, _i64, _i64, _f32, _ptr, _i64, _ptr, _i64, _f32, _ptr, _i64, _ptr, _i64, _ptr],
     "pinot_b200_gram_fwd": [_i32, _ptr, _ptr, _ptr, _i64, _ptr, _ptr, _i64, _i64, _i64, _i64, _f32, _ptr, _ptr],
     "pinot_b200_gram_bwd": [_i32, _ptr, _ptr, _ptr, _i64, _ptr, _ptr, _i64, _i64, _i64, _i64, _ptr, _ptr, _ptr, _ptr, _i32, _ptr],
     "pinot_b200_potrf_workspace_bytes": [_i64],
@@ -45,6 +47,7 @@ SIGNATURES = {
 _RESTYPES = {
     "pinot_b200_last_error": ctypes.c_char_p,
     "pinot_b200_potrf_workspace_bytes": ctypes.c_int64,
+    "pinot_b200_sgemm_nt_tma_workspace_bytes": ctypes.c_int64,
     "pinot_b200_launch_count": ctypes.c_int64,
 }
 

@@ -24,4 +24,8 @@ struct KParams {
 // gemm_tc.cu: 3xTF32 tensor-core (tcgen05 / TMEM) implementation of the same contract.
 int launch_gemm_tc(const KParams& p, bool transA, bool transB, dim3 grid, cudaStream_t stream);
 
+// gemm_tma.cu: TMA-fed NT variant working from pre-split (hi / lo) operands in caller-provided scratch.
+int64_t gemm_tma_scratch_floats(int64_t M, int64_t N, int64_t K, bool same_operand);
+int launch_gemm_tma(const KParams& p, float* scratch, bool same_operand, cudaStream_t stream);
+
 }  // namespace pb

@@ -1,0 +1,376 @@
+// TMA-fed, warp-specialised tcgen05 GEMM for LARGE products  C = alpha A B^T (+ beta C ...)  with A (M x K)
+// and B (N x K) both K-contiguous ("NT").
+//
+// The register-staged kernel in gemm_tc.cu spends its instruction-issue budget on loading,
+// splitting (3xTF32) and storing operands -- every CTA of a tile row re-splits the same A slab.
+// Here the split happens ONCE per operand, in a memory-bound pre-pass into caller-provided scratch
+// (a_hi, a_lo, b_hi, b_lo: tf32-valued fp32 arrays), and the GEMM itself contains no loader code:
+//   warp 0   one thread issues cp.async.bulk.tensor (TMA) loads of 128 x 32 tiles of the four arrays
+//            into a 3-stage ring of 128B-swizzled shared-memory tiles (64 KB per stage);
+//   warp 1   one thread issues tcgen05.mma.kind::tf32 (M = 128, N = 128, K = 8; 12 per stage:
+//            lo.hi + hi.lo into the cross-term accumulator, hi.hi into the main one) and releases
+//            each stage with tcgen05.commit;
+//   warps 2-5 drain the accumulators: tcgen05.ld, transpose through shared memory, fused epilogue.
+// The accumulators are double-buffered in TMEM (2 x 256 columns) and swapped every 512 K-columns
+// (TMEM accumulation truncates, see gemm_tc.cu), so flushing chunk c overlaps the MMAs of chunk c+1.
+#include "gemm_params.cuh"
+#include "gemm_epilogue.cuh"
+#include <cuda.h>
+#include "../../include/pinot_b200.h"
+#include <stdlib.h>
+
+namespace pb {
+
+namespace {
+
+constexpr int BM = 128, BN = 128, BK = 32, NSTAGE = 3;
+constexpr int TILE_BYTES = BM * BK * 4;            // 16 KB: 128 rows x 128 bytes, SWIZZLE_128B
+constexpr int STAGE_BYTES = 4 * TILE_BYTES;        // a_hi | a_lo | b_hi | b_lo
+constexpr int EPI_BYTES = 4 * 32 * EPI_LD * 4;     // one 32x32 staging tile per epilogue warp
+constexpr int SMEM_BYTES = NSTAGE * STAGE_BYTES + EPI_BYTES + 1024;
+constexpr int NTHREADS = 192;                      // producer, MMA, 4 epilogue warps
+constexpr int KCHUNK = 512;
+constexpr int STAGES_PER_CHUNK = KCHUNK / BK;
+
+__device__ __forceinline__ uint32_t s32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE;\n\t"
+        "bra WAIT_LOOP;\n\t"
+        "DONE:\n\t"
+        "}\n" ::"r"(s32(bar)), "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(s32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int x, int y, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+            s32(dst)),
+        "l"(map), "r"(x), "r"(y), "r"(s32(bar))
+        : "memory");
+}
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (8 rows x 128 B atoms, SBO = 1024 B).
+__device__ __forceinline__ uint64_t sw128_desc(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+    d |= (uint64_t)1 << 16;                 // LBO: unused for swizzled K-major layouts
+    d |= (uint64_t)(1024 >> 4) << 32;       // SBO
+    d |= (uint64_t)1 << 46;                 // descriptor version (sm_100)
+    d |= (uint64_t)2 << 61;                 // SWIZZLE_128B
+    return d;
+}
+__device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "}\n" ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void mma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(s32(bar)) : "memory");
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(NTHREADS, 1)
+tgemm_tma_kernel(const KParams p, const __grid_constant__ CUtensorMap map_ah, const __grid_constant__ CUtensorMap map_al,
+                 const __grid_constant__ CUtensorMap map_bh, const __grid_constant__ CUtensorMap map_bl) {
+    extern __shared__ __align__(1024) uint8_t dyn_smem[];
+    __shared__ __align__(8) uint64_t full_bar[NSTAGE], empty_bar[NSTAGE], acc_full[2], acc_empty[2];
+    __shared__ uint32_t tmem_base_holder;
+
+    const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+    if (p.lower && n0 > m0 + BM - 1) return;
+    int kb = 0;
+    const int ke = p.K;
+    if (p.ktri) kb = (m0 / BK) * BK;
+    const int num_k = (ke > kb) ? (ke - kb + BK - 1) / BK : 0;
+    const int num_chunks = num_k > 0 ? (num_k + STAGES_PER_CHUNK - 1) / STAGES_PER_CHUNK : 1;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dyn_smem) + 1023) & ~(uintptr_t)1023);
+    float* epi_smem = reinterpret_cast<float*>(smem + NSTAGE * STAGE_BYTES);
+
+    if (tid == 0) {
+        for (int s = 0; s < NSTAGE; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&acc_full[s], 1);
+            mbar_init(&acc_empty[s], 128);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_ah) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_al) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_bh) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_bl) : "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(&tmem_base_holder)),
+                     "r"(512u)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_d = tmem_base_holder;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            for (int kt = 0; kt < num_k; ++kt) {
+                const int s = kt % NSTAGE;
+                if (kt >= NSTAGE) mbar_wait(&empty_bar[s], (uint32_t)((kt / NSTAGE - 1) & 1));
+                uint8_t* st = smem + s * STAGE_BYTES;
+                mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                const int kc = kb + kt * BK;
+                tma_load_2d(st, &map_ah, kc, m0, &full_bar[s]);
+                tma_load_2d(st + TILE_BYTES, &map_al, kc, m0, &full_bar[s]);
+                tma_load_2d(st + 2 * TILE_BYTES, &map_bh, kc, n0, &full_bar[s]);
+                tma_load_2d(st + 3 * TILE_BYTES, &map_bl, kc, n0, &full_bar[s]);
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+            for (int chunk = 0; chunk < num_chunks; ++chunk) {
+                const int set = chunk & 1;
+                if (chunk >= 2) mbar_wait(&acc_empty[set], (uint32_t)((chunk / 2 - 1) & 1));
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t acc_hi = tmem_d + (uint32_t)(set * 256), acc_x = acc_hi + 128u;
+                const int kt_beg = chunk * STAGES_PER_CHUNK, kt_end = min(num_k, kt_beg + STAGES_PER_CHUNK);
+                for (int kt = kt_beg; kt < kt_end; ++kt) {
+                    const int s = kt % NSTAGE;
+                    mbar_wait(&full_bar[s], (uint32_t)((kt / NSTAGE) & 1));
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t sb = s32(smem + s * STAGE_BYTES);
+                    const uint64_t d_ah = sw128_desc(sb), d_al = sw128_desc(sb + TILE_BYTES);
+                    const uint64_t d_bh = sw128_desc(sb + 2 * TILE_BYTES), d_bl = sw128_desc(sb + 3 * TILE_BYTES);
+#pragma unroll
+                    for (int k8 = 0; k8 < BK / 8; ++k8) {
+                        const uint64_t adv = (uint64_t)((k8 * 32) >> 4);   // +32 bytes inside the swizzle atom
+                        const uint32_t acc = (kt > kt_beg || k8 > 0) ? 1u : 0u;
+                        mma_tf32(acc_x, d_al + adv, d_bh + adv, idesc, acc);
+                        mma_tf32(acc_x, d_ah + adv, d_bl + adv, idesc, 1u);
+                        mma_tf32(acc_hi, d_ah + adv, d_bh + adv, idesc, acc);
+                    }
+                    mma_commit(&empty_bar[s]);     // stage free once these MMAs have read it
+                }
+                mma_commit(&acc_full[set]);        // accumulators of this chunk complete
+            }
+        }
+    } else {
+        // ===================== epilogue warps =====================
+        float alpha = p.alpha, r1c = p.r1coef;
+        if (p.alpha_dev) {
+            const float s = __ldg(p.alpha_dev);
+            alpha *= s;
+            r1c *= s;
+        }
+        const int q = warp & 3;                       // TMEM lane quadrant this warp may access
+        float* tile = epi_smem + (warp - 2) * (32 * EPI_LD);
+        for (int chunk = 0; chunk < num_chunks; ++chunk) {
+            const int set = chunk & 1;
+            const bool last_chunk = (chunk == num_chunks - 1);
+            const float beta = (chunk == 0) ? p.beta : 1.f;
+            if (num_k > 0) mbar_wait(&acc_full[set], (uint32_t)((chunk / 2) & 1));
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll 1
+            for (int c0 = 0; c0 < BN; c0 += 32) {
+                uint32_t v[32], w[32];
+                if (num_k > 0) {
+                    const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(set * 256 + c0);
+                    asm volatile(
+                        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+                        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                        : "r"(taddr)
+                        : "memory");
+                    asm volatile(
+                        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+                        : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]),
+                          "=r"(w[8]), "=r"(w[9]), "=r"(w[10]), "=r"(w[11]), "=r"(w[12]), "=r"(w[13]), "=r"(w[14]), "=r"(w[15]),
+                          "=r"(w[16]), "=r"(w[17]), "=r"(w[18]), "=r"(w[19]), "=r"(w[20]), "=r"(w[21]), "=r"(w[22]), "=r"(w[23]),
+                          "=r"(w[24]), "=r"(w[25]), "=r"(w[26]), "=r"(w[27]), "=r"(w[28]), "=r"(w[29]), "=r"(w[30]), "=r"(w[31])
+                        : "r"(taddr + 128u)
+                        : "memory");
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) { v[j] = 0u; w[j] = 0u; }
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    float4 t;
+                    t.x = __uint_as_float(v[4 * i + 0]) + __uint_as_float(w[4 * i + 0]);
+                    t.y = __uint_as_float(v[4 * i + 1]) + __uint_as_float(w[4 * i + 1]);
+                    t.z = __uint_as_float(v[4 * i + 2]) + __uint_as_float(w[4 * i + 2]);
+                    t.w = __uint_as_float(v[4 * i + 3]) + __uint_as_float(w[4 * i + 3]);
+                    *reinterpret_cast<float4*>(tile + lane * EPI_LD + 4 * i) = t;
+                }
+                __syncwarp();
+                epilogue_rows<EPI>(p, tile, alpha, beta, r1c, last_chunk, m0, n0, q, c0, lane);
+                __syncwarp();
+            }
+            // this accumulator set may be overwritten by chunk + 2
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            mbar_arrive(&acc_empty[set]);
+        }
+    }
+
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(512u) : "memory");
+    }
+}
+
+// hi = rna_tf32(x * scale[col]), lo = rna_tf32(x * scale[col] - hi); 16-byte accesses.
+__global__ void __launch_bounds__(256)
+split_tf32_kernel(const float* __restrict__ x, int64_t ldx, float* __restrict__ hi, float* __restrict__ lo, int64_t ldo,
+                  int64_t rows, int cols4, const float* __restrict__ colscale) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t r = t / cols4;
+    if (r >= rows) return;
+    const int c = (int)(t - r * cols4) * 4;
+    float4 v = __ldg(reinterpret_cast<const float4*>(x + r * ldx + c));
+    if (colscale) {
+        const float4 s = __ldg(reinterpret_cast<const float4*>(colscale + c));
+        v.x *= s.x; v.y *= s.y; v.z *= s.z; v.w *= s.w;
+    }
+    float4 h, l;
+    uint32_t u;
+#define PB_SPLIT(F)                                                       \
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(v.F));                 \
+    h.F = __uint_as_float(u);                                             \
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(v.F - h.F));           \
+    l.F = __uint_as_float(u);
+    PB_SPLIT(x) PB_SPLIT(y) PB_SPLIT(z) PB_SPLIT(w)
+#undef PB_SPLIT
+    *reinterpret_cast<float4*>(hi + r * ldo + c) = h;
+    *reinterpret_cast<float4*>(lo + r * ldo + c) = l;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = [] {
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            f = nullptr;
+        return reinterpret_cast<EncodeTiledFn>(f);
+    }();
+    return fn;
+}
+
+// 2-D map over a row-major fp32 array (rows x cols, leading dimension ld): box = 32 columns x 128 rows.
+int make_map(CUtensorMap* map, const float* base, int64_t rows, int64_t cols, int64_t ld) {
+    EncodeTiledFn fn = encode_fn();
+    PB_REQUIRE(fn != nullptr, "gemm (TMA): cuTensorMapEncodeTiled is not available from this driver");
+    const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+    const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)BM};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult rc = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    PB_REQUIRE(rc == CUDA_SUCCESS, "gemm (TMA): cuTensorMapEncodeTiled failed with code %d", (int)rc);
+    return PB_OK;
+}
+
+}  // namespace
+
+int64_t gemm_tma_scratch_floats(int64_t M, int64_t N, int64_t K, bool same_operand) {
+    const int64_t ldk = (K + 3) / 4 * 4;
+    return 2 * M * ldk + (same_operand ? 0 : 2 * N * ldk);
+}
+
+int launch_gemm_tma(const KParams& p, float* scratch, bool same_operand, cudaStream_t stream) {
+    const int64_t M = p.M, N = p.N, K = p.K;
+    const int64_t ldk = (K + 3) / 4 * 4;
+    PB_REQUIRE(p.vecA && p.vecB && p.vecC && (K % 4 == 0), "gemm (TMA): operands must be 16-byte aligned with K % 4 == 0");
+    PB_REQUIRE(p.splitk == 1 && !p.post_wdiag, "gemm (TMA): split-K / look-ahead are not supported on this path");
+    float* a_hi = scratch;
+    float* a_lo = a_hi + M * ldk;
+    float* b_hi = same_operand ? a_hi : a_lo + M * ldk;
+    float* b_lo = same_operand ? a_lo : b_hi + N * ldk;
+    const int cols4 = (int)(K / 4);
+    split_tf32_kernel<<<(unsigned)ceil_div(M * cols4, 256), 256, 0, stream>>>(p.A, p.lda, a_hi, a_lo, ldk, M, cols4, p.kscale);
+    int rc = check_launch("split_tf32 (A)");
+    if (rc) return rc;
+    if (!same_operand) {
+        split_tf32_kernel<<<(unsigned)ceil_div(N * cols4, 256), 256, 0, stream>>>(p.B, p.ldb, b_hi, b_lo, ldk, N, cols4, nullptr);
+        rc = check_launch("split_tf32 (B)");
+        if (rc) return rc;
+    }
+    alignas(64) CUtensorMap mah, mal, mbh, mbl;
+    if ((rc = make_map(&mah, a_hi, M, K, ldk))) return rc;
+    if ((rc = make_map(&mal, a_lo, M, K, ldk))) return rc;
+    if ((rc = make_map(&mbh, b_hi, N, K, ldk))) return rc;
+    if ((rc = make_map(&mbl, b_lo, N, K, ldk))) return rc;
+    dim3 grid((unsigned)ceil_div(N, BN), (unsigned)ceil_div(M, BM), 1);
+    auto launch = [&](auto kern) -> int {
+        PB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        kern<<<grid, NTHREADS, SMEM_BYTES, stream>>>(p, mah, mal, mbh, mbl);
+        return check_launch("gemm (tcgen05 + TMA)");
+    };
+    if (p.r1u || p.mirror) return launch(tgemm_tma_kernel<2>);
+    if (p.act) return launch(tgemm_tma_kernel<1>);
+    return launch(tgemm_tma_kernel<0>);
+}
+
+}  // namespace pb
+
+extern "C" {
+
+int64_t pinot_b200_sgemm_nt_tma_workspace_bytes(int64_t M, int64_t N, int64_t K) {
+    if (M < 0 || N < 0 || K < 0) return -1;
+    return pb::gemm_tma_scratch_floats(M, N, K, false) * (int64_t)sizeof(float);
+}
+
+int pinot_b200_sgemm_nt_tma(int64_t M, int64_t N, int64_t K, float alpha, const float* A, int64_t lda, const float* B,
+                            int64_t ldb, float beta, float* C, int64_t ldc, void* workspace, int64_t workspace_bytes,
+                            cudaStream_t stream) {
+    PB_REQUIRE(M > 0 && N > 0 && K > 0, "sgemm_nt_tma: empty product");
+    PB_REQUIRE(M < (1ll << 31) && N < (1ll << 31) && K < (1ll << 31), "sgemm_nt_tma: size exceeds int32");
+    PB_REQUIRE(A && B && C && workspace, "sgemm_nt_tma: null pointer");
+    PB_REQUIRE(workspace_bytes >= pinot_b200_sgemm_nt_tma_workspace_bytes(M, N, K),
+               "sgemm_nt_tma: workspace too small (%lld bytes given)", (long long)workspace_bytes);
+    auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+    PB_REQUIRE(K % 4 == 0 && lda % 4 == 0 && ldb % 4 == 0 && ldc % 4 == 0 && al16(A) && al16(B) && al16(C) && al16(workspace),
+               "sgemm_nt_tma: operands must be 16-byte aligned with K and leading dimensions multiples of 4");
+    pb::KParams p{};
+    p.M = (int)M; p.N = (int)N; p.K = (int)K;
+    p.A = A; p.lda = lda; p.B = B; p.ldb = ldb; p.C = C; p.ldc = ldc;
+    p.alpha = alpha; p.beta = beta; p.splitk = 1; p.vecA = p.vecB = p.vecC = 1;
+    return pb::launch_gemm_tma(p, static_cast<float*>(workspace), false, stream);
+}
+
+}  // extern "C"
+
