@@ -138,13 +138,18 @@ PINOT_B200_API int pinot_b200_gram_bwd(int kind, const float* x, const float* y,
  *   X (r x n)                       -> X L^{-T}
  * r = n_ext_dense (+ n if ext_identity: the caller stores I in those rows and gets L^{-T} back;
  * they must FOLLOW the dense rows).  diag_out (n, optional) receives diag(L).  *info (device int)
- * is 0 on success or 1 + the first non-positive pivot (LAPACK convention).  workspace must hold
- * pinot_b200_potrf_workspace_bytes(n) bytes.
+ * is 0 on success or 1 + the first non-positive pivot (LAPACK convention).  workspace (16-byte
+ * aligned, workspace_bytes long) must hold at least pinot_b200_potrf_workspace_bytes(n) bytes; when
+ * it holds pinot_b200_potrf_tma_scratch_bytes(n, n_ext_dense) MORE, the rank-512 trailing updates of
+ * large factorisations (n >= 6144) run on the TMA-fed tensor-core kernel from hi / lo panel copies
+ * kept in that tail (same arithmetic, same results).
  * Replaces torch.cholesky + torch.triangular_solve at gaussian_process_regressor.py:108-119,215,373-390.
  * --------------------------------------------------------------------------------------------- */
 PINOT_B200_API int64_t pinot_b200_potrf_workspace_bytes(int64_t n);
+PINOT_B200_API int64_t pinot_b200_potrf_tma_scratch_bytes(int64_t n, int64_t n_ext_dense);
 PINOT_B200_API int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, int ext_identity,
-                         float* diag_out, void* workspace, int* info, cudaStream_t stream);
+                         float* diag_out, void* workspace, int64_t workspace_bytes, int* info,
+                         cudaStream_t stream);
 /* The same sweep as pinot_b200_potrf_ext for callers that cannot hand over scratch memory.
  * (No counterpart in the reference: pinot lets torch allocate whatever cuSOLVER asks for.)
  *
@@ -187,10 +192,14 @@ PINOT_B200_API int pinot_b200_gp_nll(const float* diag_l, const float* z, int64_
  * given): 0.5 L^{-T} diag(L) L^{-1} - 0.5 alpha alpha^T   (exact_logdet = 0, trace(L) objective)
  *         0.5 K^{-1}                 - 0.5 alpha alpha^T   (exact_logdet = 1).
  * linv_t = L^{-T} (upper triangular, from the identity extension rows of the sweep).
+ * workspace is optional (NULL / 0): given pinot_b200_gp_nll_grad_workspace_bytes(n) bytes (0 for
+ * small n), the product runs on the TMA-fed tensor-core kernel from a pre-split copy of
+ * L^{-T} diag(L)^{1/2}; without it the register-staged kernel is used.
  * Replaces autograd's cholesky_backward / triangular_solve_backward for :123-166. */
+PINOT_B200_API int64_t pinot_b200_gp_nll_grad_workspace_bytes(int64_t n);
 PINOT_B200_API int pinot_b200_gp_nll_grad(const float* linv_t, int64_t ld, int64_t n, const float* diag_l,
                            const float* alpha, const float* upstream, int exact_logdet, float* dk,
-                           int64_t lddk, cudaStream_t stream);
+                           int64_t lddk, void* workspace, int64_t workspace_bytes, cudaStream_t stream);
 /* Predictive marginals from vt = K_te,tr L^{-T} (n_te x n) and z = L^{-1} y:
  * mean[i] = vt[i,:].z ; var[i] = exp(*variance) + eps - |vt[i,:]|^2  (var may be NULL).
  * Equals the mean and the diagonal of the covariance at gaussian_process_regressor.py:212-221. */

@@ -35,19 +35,23 @@ SIGNATURES = {
     "pinot_b200_gram_fwd": [_i32, _ptr, _ptr, _ptr, _i64, _ptr, _ptr, _i64, _i64, _i64, _i64, _f32, _ptr, _ptr],
     "pinot_b200_gram_bwd": [_i32, _ptr, _ptr, _ptr, _i64, _ptr, _ptr, _i64, _i64, _i64, _i64, _ptr, _ptr, _ptr, _ptr, _i32, _ptr],
     "pinot_b200_potrf_workspace_bytes": [_i64],
-    "pinot_b200_potrf_ext": [_ptr, _i64, _i64, _i64, _i32, _ptr, _ptr, _ptr, _ptr],
+    "pinot_b200_potrf_tma_scratch_bytes": [_i64, _i64],
+    "pinot_b200_potrf_ext": [_ptr, _i64, _i64, _i64, _i32, _ptr, _ptr, _i64, _ptr, _ptr],
     "pinot_b200_potrf_ext_noalloc": [_ptr, _i64, _i64, _i64, _i32, _ptr, _ptr, _ptr],
     "pinot_b200_trsm_rlt": [_ptr, _i64, _i64, _ptr, _i64, _i64, _ptr],
     "pinot_b200_zero_upper": [_ptr, _i64, _i64, _ptr],
     "pinot_b200_gemv_rows": [_ptr, _i64, _i64, _i64, _i32, _ptr, _ptr, _ptr],
     "pinot_b200_gp_nll": [_ptr, _ptr, _i64, _ptr, _ptr],
-    "pinot_b200_gp_nll_grad": [_ptr, _i64, _i64, _ptr, _ptr, _ptr, _i32, _ptr, _i64, _ptr],
+    "pinot_b200_gp_nll_grad_workspace_bytes": [_i64],
+    "pinot_b200_gp_nll_grad": [_ptr, _i64, _i64, _ptr, _ptr, _ptr, _i32, _ptr, _i64, _ptr, _i64, _ptr],
     "pinot_b200_gp_predict_mean_var": [_ptr, _i64, _i64, _i64, _ptr, _ptr, _f32, _ptr, _ptr, _ptr],
 }
 _RESTYPES = {
     "pinot_b200_last_error": ctypes.c_char_p,
     "pinot_b200_potrf_workspace_bytes": ctypes.c_int64,
     "pinot_b200_sgemm_nt_tma_workspace_bytes": ctypes.c_int64,
+    "pinot_b200_potrf_tma_scratch_bytes": ctypes.c_int64,
+    "pinot_b200_gp_nll_grad_workspace_bytes": ctypes.c_int64,
     "pinot_b200_launch_count": ctypes.c_int64,
 }
 
@@ -125,5 +129,14 @@ def launch_count():
     return int(load().pinot_b200_launch_count())
 
 
-def potrf_workspace_bytes(n):
-    return int(load().pinot_b200_potrf_workspace_bytes(int(n)))
+def potrf_workspace_bytes(n, n_ext_dense=None):
+    """Minimum sweep workspace; with n_ext_dense given, including the TMA scratch tail (0 for small n)."""
+    lib = load()
+    base = int(lib.pinot_b200_potrf_workspace_bytes(int(n)))
+    if n_ext_dense is None:
+        return base
+    return base + int(lib.pinot_b200_potrf_tma_scratch_bytes(int(n), int(n_ext_dense)))
+
+
+def gp_nll_grad_workspace_bytes(n):
+    return int(load().pinot_b200_gp_nll_grad_workspace_bytes(int(n)))

@@ -14,6 +14,7 @@
 // V^T = K_te,tr L^{-T} (all that the predictive distribution needs).  Identity extension rows are
 // only touched from the column block where their 1 sits, so L^{-T} costs n^3/3 extra flops.
 #include "gemm.cuh"
+#include "gemm_params.cuh"
 #include "chol_diag.cuh"
 #include <stdlib.h>
 #include "../../include/pinot_b200.h"
@@ -23,6 +24,8 @@
 namespace {
 
 constexpr int NB = 64;        // panel width
+constexpr int64_t TMA_SPLIT_COLS = 128;   // tile column 0 of a rank-W update stays on the look-ahead kernel
+constexpr int64_t TMA_MIN_N = 1024;       // below this the pre-split pass costs more than it saves
 constexpr int LDL = NB + 4;   // shared stride of the diagonal block
 constexpr int PR = 256;       // panel rows per CTA (one thread per row)
 constexpr int LDT = NB + 1;   // shared stride of the staged panel rows
@@ -325,17 +328,37 @@ int64_t pinot_b200_potrf_workspace_bytes(int64_t n) {
     return (int64_t)sizeof(float) * nblk * NB * NB * 2 + pb::ceil_div(nblk * (int64_t)sizeof(int), 256) * 256;
 }
 
+int64_t pinot_b200_potrf_tma_scratch_bytes(int64_t n, int64_t n_ext_dense) {
+    if (n < 0 || n_ext_dense < 0) return -1;
+    const int64_t W = outer_block_width(n);
+    if (W <= NB || !pb::gemm_tma_enabled()) return 0;   // single-level sweep: no rank-W updates
+    // hi / lo copies of one (n + n_ext_dense) x W panel
+    return (int64_t)sizeof(float) * 2 * (n + n_ext_dense) * W;
+}
+
 int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, int ext_identity,
-                         float* diag_out, void* workspace, int* info, cudaStream_t stream) {
+                         float* diag_out, void* workspace, int64_t workspace_bytes, int* info,
+                         cudaStream_t stream) {
     PB_REQUIRE(n >= 0 && n < (1ll << 30) && n_ext_dense >= 0 && ld >= n, "potrf_ext: invalid sizes");
     PB_REQUIRE(info, "potrf_ext: info pointer is required");
     PB_CUDA(cudaMemsetAsync(info, 0, sizeof(int), stream));
     if (n == 0) return pb::PB_OK;
     PB_REQUIRE(e && workspace, "potrf_ext: null pointer");
+    const int64_t base_bytes = pinot_b200_potrf_workspace_bytes(n);
+    PB_REQUIRE(workspace_bytes >= base_bytes, "potrf_ext: workspace of %lld bytes is smaller than the %lld required",
+               (long long)workspace_bytes, (long long)base_bytes);
     const int64_t nblk = pb::ceil_div(n, NB);
     float* wdiag = static_cast<float*>(workspace);
     float* winv = wdiag + nblk * NB * NB;
     int* flags = reinterpret_cast<int*>(winv + nblk * NB * NB);
+    // optional tail of the workspace: hi / lo panel copies for the TMA-fed rank-W updates
+    float* tma_scratch = nullptr;
+    {
+        const int64_t extra = pinot_b200_potrf_tma_scratch_bytes(n, n_ext_dense);
+        if (extra > 0 && workspace_bytes >= base_bytes + extra && (ld % 4 == 0) && pb::aligned16(e) &&
+            pb::aligned16(workspace))
+            tma_scratch = reinterpret_cast<float*>(static_cast<char*>(workspace) + base_bytes);
+    }
     PB_CUDA(cudaMemsetAsync(flags, 0, sizeof(int) * nblk, stream));
     const int64_t r_total = n_ext_dense + (ext_identity ? n : 0);
     // the fused look-ahead kernel is built for 16-byte aligned rows only (ld % 4 == 0)
@@ -404,7 +427,34 @@ int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, i
             }
         }
         // (d) rank-(J1 - J0) update of everything to the right of the outer block
-        if (J1 < n) {
+        if (J1 < n && tma_scratch && lookahead && (n - J1) > 2 * TMA_SPLIT_COLS) {
+            // Same update in two launches that share the panel: tile column 0 (which carries the
+            // look-ahead factor + panel solve) with the register-staged kernel, everything to its
+            // right with the TMA-fed kernel working from one hi / lo copy of the panel.
+            const int64_t row_end = active_rows_end(J1);
+            const int64_t rows = row_end - J1, K = J1 - J0, ldk = (K + 3) / 4 * 4;
+            PB_REQUIRE(rows <= n + n_ext_dense, "potrf_ext: internal error (panel of %lld rows)", (long long)rows);
+            float* hi = tma_scratch;
+            float* lo = hi + rows * ldk;
+            int rc = pb::tma_split_operand(e + J1 * ld + J0, ld, rows, K, hi, lo, nullptr, 0, 0, stream);
+            if (rc) return rc;
+            pb::GemmParams g;
+            g.M = (int)rows; g.N = (int)TMA_SPLIT_COLS; g.K = (int)K;
+            g.A = e + J1 * ld + J0; g.lda = ld; g.transA = false;
+            g.B = e + J1 * ld + J0; g.ldb = ld; g.transB = true;
+            g.C = e + J1 * ld + J1; g.ldc = ld;
+            g.alpha = -1.f; g.beta = 1.f; g.lower = 1;
+            attach_lookahead(g, J1);
+            rc = pb::gemm(g, stream);
+            if (rc) return rc;
+            const int64_t o = TMA_SPLIT_COLS;
+            pb::KParams p{};
+            p.M = (int)(rows - o); p.N = (int)(n - J1 - o); p.K = (int)K;
+            p.C = e + (J1 + o) * ld + (J1 + o); p.ldc = ld;
+            p.alpha = -1.f; p.beta = 1.f; p.lower = 1; p.splitk = 1; p.vecC = 1;
+            rc = pb::launch_gemm_tma_presplit(p, hi + o * ldk, lo + o * ldk, hi + o * ldk, lo + o * ldk, stream);
+            if (rc) return rc;
+        } else if (J1 < n) {
             const int64_t row_end = active_rows_end(J1);
             pb::GemmParams g;
             g.M = (int)(row_end - J1); g.N = (int)(n - J1); g.K = (int)(J1 - J0);
@@ -554,14 +604,41 @@ int pinot_b200_gemv_rows(const float* m, int64_t ld, int64_t rows, int64_t cols,
     return pb::check_launch("gemv_rows");
 }
 
+int64_t pinot_b200_gp_nll_grad_workspace_bytes(int64_t n) {
+    if (n < 0) return -1;
+    if (n < TMA_MIN_N || !pb::gemm_tma_enabled()) return 0;
+    return (int64_t)sizeof(float) * 2 * n * ((n + 3) / 4 * 4);   // hi / lo copies of L^{-T} diag(L)^{1/2}
+}
+
 int pinot_b200_gp_nll_grad(const float* linv_t, int64_t ld, int64_t n, const float* diag_l,
                            const float* alpha, const float* upstream, int exact_logdet, float* dk,
-                           int64_t lddk, cudaStream_t stream) {
+                           int64_t lddk, void* workspace, int64_t workspace_bytes, cudaStream_t stream) {
     // dNLL/dK = 0.5 L^{-T} diag(L) L^{-1} - 0.5 alpha alpha^T      (trace(L) objective)
     //         = 0.5 L^{-T} L^{-1}         - 0.5 alpha alpha^T      (exact log-det objective)
     PB_REQUIRE(n >= 0 && n < (1ll << 31) && ld >= n && lddk >= n, "gp_nll_grad: invalid sizes");
     if (n == 0) return pb::PB_OK;
     PB_REQUIRE(linv_t && alpha && dk && (exact_logdet || diag_l), "gp_nll_grad: null pointer");
+    {
+        // Large n with a workspace: split W = L^{-T} diag(L)^{1/2} once (same operand on both sides of
+        // W W^T) and run the TMA-fed tensor-core kernel on it.
+        const int64_t need = pinot_b200_gp_nll_grad_workspace_bytes(n);
+        const int64_t n4 = (n + 3) / 4 * 4;
+        if (need > 0 && workspace && workspace_bytes >= need && ld % 4 == 0 && ld >= n4 && lddk % 4 == 0 &&
+            pb::aligned16(linv_t) && pb::aligned16(dk) && pb::aligned16(workspace) &&
+            (exact_logdet || pb::aligned16(diag_l))) {
+            float* hi = static_cast<float*>(workspace);
+            float* lo = hi + n * n4;
+            int rc = pb::tma_split_operand(linv_t, ld, n, n, hi, lo, diag_l, exact_logdet ? 0 : 2, 1, stream);
+            if (rc) return rc;
+            pb::KParams p{};
+            p.M = p.N = p.K = (int)n;
+            p.C = dk; p.ldc = lddk;
+            p.alpha = 0.5f; p.beta = 0.f; p.alpha_dev = upstream;
+            p.r1u = alpha; p.r1v = alpha; p.r1coef = -0.5f;
+            p.lower = 1; p.mirror = 1; p.ktri = 1; p.splitk = 1; p.vecC = 1;
+            return pb::launch_gemm_tma_presplit(p, hi, lo, hi, lo, stream);
+        }
+    }
     pb::GemmParams g;
     g.M = (int)n; g.N = (int)n; g.K = (int)n;
     g.A = linv_t; g.lda = ld; g.transA = false;

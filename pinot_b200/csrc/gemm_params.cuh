@@ -27,5 +27,12 @@ int launch_gemm_tc(const KParams& p, bool transA, bool transB, dim3 grid, cudaSt
 // gemm_tma.cu: TMA-fed NT variant working from pre-split (hi / lo) operands in caller-provided scratch.
 int64_t gemm_tma_scratch_floats(int64_t M, int64_t N, int64_t K, bool same_operand);
 int launch_gemm_tma(const KParams& p, float* scratch, bool same_operand, cudaStream_t stream);
+bool gemm_tma_enabled();   // tensor-core GEMMs selected and PINOT_B200_TMA != 0
+// one operand (rows x K, row-major) -> hi / lo arrays with leading dimension ceil4(K); scale_mode 0 none,
+// 1 = columns * colscale, 2 = columns * sqrt(colscale); tri: upper-triangular operand of a ktri product
+int tma_split_operand(const float* x, int64_t ldx, int64_t rows, int64_t K, float* hi, float* lo, const float* colscale,
+                      int scale_mode, int tri, cudaStream_t stream);
+int launch_gemm_tma_presplit(const KParams& p, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo,
+                             cudaStream_t stream);
 
 }  // namespace pb

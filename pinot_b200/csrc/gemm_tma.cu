@@ -247,17 +247,21 @@ tgemm_tma_kernel(const KParams p, const __grid_constant__ CUtensorMap map_ah, co
     }
 }
 
-// hi = rna_tf32(x * scale[col]), lo = rna_tf32(x * scale[col] - hi); 16-byte accesses.
+// hi = rna_tf32(v), lo = rna_tf32(v - hi) with v = x * f(scale[col]); f = identity (mode 1) or sqrt (mode 2: the
+// same-operand form of A diag(s) A^T).  tri != 0: x is upper triangular and only columns >= the origin of the
+// row's 128-row tile are ever loaded by the GEMM (ktri), so the rest is neither read nor written.
 __global__ void __launch_bounds__(256)
 split_tf32_kernel(const float* __restrict__ x, int64_t ldx, float* __restrict__ hi, float* __restrict__ lo, int64_t ldo,
-                  int64_t rows, int cols4, const float* __restrict__ colscale) {
+                  int64_t rows, int cols4, const float* __restrict__ colscale, int scale_mode, int tri) {
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t r = t / cols4;
     if (r >= rows) return;
     const int c = (int)(t - r * cols4) * 4;
+    if (tri && c + 4 <= (int)((r / BM) * BM)) return;
     float4 v = __ldg(reinterpret_cast<const float4*>(x + r * ldx + c));
-    if (colscale) {
-        const float4 s = __ldg(reinterpret_cast<const float4*>(colscale + c));
+    if (scale_mode) {
+        float4 s = __ldg(reinterpret_cast<const float4*>(colscale + c));
+        if (scale_mode == 2) { s.x = sqrtf(s.x); s.y = sqrtf(s.y); s.z = sqrtf(s.z); s.w = sqrtf(s.w); }
         v.x *= s.x; v.y *= s.y; v.z *= s.z; v.w *= s.w;
     }
     float4 h, l;
@@ -311,30 +315,42 @@ int64_t gemm_tma_scratch_floats(int64_t M, int64_t N, int64_t K, bool same_opera
     return 2 * M * ldk + (same_operand ? 0 : 2 * N * ldk);
 }
 
-int launch_gemm_tma(const KParams& p, float* scratch, bool same_operand, cudaStream_t stream) {
+bool gemm_tma_enabled() {
+    static const bool on = [] {
+        const char* e = getenv("PINOT_B200_TMA");
+        return !(e && e[0] == '0');
+    }();
+    return on && gemm_uses_tensor_cores();
+}
+
+int tma_split_operand(const float* x, int64_t ldx, int64_t rows, int64_t K, float* hi, float* lo, const float* colscale,
+                      int scale_mode, int tri, cudaStream_t stream) {
+    const int64_t ldk = (K + 3) / 4 * 4;
+    PB_REQUIRE(ldx % 4 == 0 && ldx >= ldk && aligned16(x) && aligned16(hi) && aligned16(lo),
+               "gemm (TMA): operand rows must be 16-byte aligned and padded to a multiple of 4 columns");
+    PB_REQUIRE(scale_mode == 0 || (colscale && aligned16(colscale)), "gemm (TMA): column scale must be 16-byte aligned");
+    const int cols4 = (int)(ldk / 4);
+    split_tf32_kernel<<<(unsigned)ceil_div(rows * cols4, 256), 256, 0, stream>>>(x, ldx, hi, lo, ldk, rows, cols4, colscale,
+                                                                                 scale_mode, tri);
+    return check_launch("split_tf32");
+}
+
+// C (M x N) = alpha A B^T (+ ...) from pre-split operands: a_* (M x K), b_* (N x K), leading dimension ceil4(K).
+int launch_gemm_tma_presplit(const KParams& p, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo,
+                             cudaStream_t stream) {
     const int64_t M = p.M, N = p.N, K = p.K;
     const int64_t ldk = (K + 3) / 4 * 4;
-    PB_REQUIRE(p.vecA && p.vecB && p.vecC && (K % 4 == 0), "gemm (TMA): operands must be 16-byte aligned with K % 4 == 0");
+    PB_REQUIRE(p.vecC && p.ldc % 4 == 0 && aligned16(p.C), "gemm (TMA): C must be 16-byte aligned with ldc % 4 == 0");
     PB_REQUIRE(p.splitk == 1 && !p.post_wdiag, "gemm (TMA): split-K / look-ahead are not supported on this path");
-    float* a_hi = scratch;
-    float* a_lo = a_hi + M * ldk;
-    float* b_hi = same_operand ? a_hi : a_lo + M * ldk;
-    float* b_lo = same_operand ? a_lo : b_hi + N * ldk;
-    const int cols4 = (int)(K / 4);
-    split_tf32_kernel<<<(unsigned)ceil_div(M * cols4, 256), 256, 0, stream>>>(p.A, p.lda, a_hi, a_lo, ldk, M, cols4, p.kscale);
-    int rc = check_launch("split_tf32 (A)");
-    if (rc) return rc;
-    if (!same_operand) {
-        split_tf32_kernel<<<(unsigned)ceil_div(N * cols4, 256), 256, 0, stream>>>(p.B, p.ldb, b_hi, b_lo, ldk, N, cols4, nullptr);
-        rc = check_launch("split_tf32 (B)");
-        if (rc) return rc;
-    }
+    PB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm (TMA): empty product");
     alignas(64) CUtensorMap mah, mal, mbh, mbl;
+    int rc;
     if ((rc = make_map(&mah, a_hi, M, K, ldk))) return rc;
     if ((rc = make_map(&mal, a_lo, M, K, ldk))) return rc;
     if ((rc = make_map(&mbh, b_hi, N, K, ldk))) return rc;
     if ((rc = make_map(&mbl, b_lo, N, K, ldk))) return rc;
     dim3 grid((unsigned)ceil_div(N, BN), (unsigned)ceil_div(M, BM), 1);
+    PB_REQUIRE(grid.y <= 65535, "gemm (TMA): M too large for one launch (%d rows)", p.M);
     auto launch = [&](auto kern) -> int {
         PB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
         kern<<<grid, NTHREADS, SMEM_BYTES, stream>>>(p, mah, mal, mbh, mbl);
@@ -343,6 +359,22 @@ int launch_gemm_tma(const KParams& p, float* scratch, bool same_operand, cudaStr
     if (p.r1u || p.mirror) return launch(tgemm_tma_kernel<2>);
     if (p.act) return launch(tgemm_tma_kernel<1>);
     return launch(tgemm_tma_kernel<0>);
+}
+
+int launch_gemm_tma(const KParams& p, float* scratch, bool same_operand, cudaStream_t stream) {
+    const int64_t M = p.M, N = p.N, K = p.K;
+    const int64_t ldk = (K + 3) / 4 * 4;
+    float* a_hi = scratch;
+    float* a_lo = a_hi + M * ldk;
+    float* b_hi = same_operand ? a_hi : a_lo + M * ldk;
+    float* b_lo = same_operand ? a_lo : b_hi + N * ldk;
+    int rc = tma_split_operand(p.A, p.lda, M, K, a_hi, a_lo, p.kscale, p.kscale ? 1 : 0, 0, stream);
+    if (rc) return rc;
+    if (!same_operand) {
+        rc = tma_split_operand(p.B, p.ldb, N, K, b_hi, b_lo, nullptr, 0, 0, stream);
+        if (rc) return rc;
+    }
+    return launch_gemm_tma_presplit(p, a_hi, a_lo, b_hi, b_lo, stream);
 }
 
 }  // namespace pb
@@ -363,8 +395,10 @@ int pinot_b200_sgemm_nt_tma(int64_t M, int64_t N, int64_t K, float alpha, const 
     PB_REQUIRE(workspace_bytes >= pinot_b200_sgemm_nt_tma_workspace_bytes(M, N, K),
                "sgemm_nt_tma: workspace too small (%lld bytes given)", (long long)workspace_bytes);
     auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
-    PB_REQUIRE(K % 4 == 0 && lda % 4 == 0 && ldb % 4 == 0 && ldc % 4 == 0 && al16(A) && al16(B) && al16(C) && al16(workspace),
-               "sgemm_nt_tma: operands must be 16-byte aligned with K and leading dimensions multiples of 4");
+    const int64_t k4 = (K + 3) / 4 * 4;
+    PB_REQUIRE(lda % 4 == 0 && ldb % 4 == 0 && ldc % 4 == 0 && lda >= k4 && ldb >= k4 && ldc >= N && al16(A) && al16(B) &&
+                   al16(C) && al16(workspace),
+               "sgemm_nt_tma: operands must be 16-byte aligned with leading dimensions that are multiples of 4 (>= K rounded up)");
     pb::KParams p{};
     p.M = (int)M; p.N = (int)N; p.K = (int)K;
     p.A = A; p.lda = lda; p.B = B; p.ldb = ldb; p.C = C; p.ldc = ldc;

@@ -229,10 +229,11 @@ def potrf_ext_raw(e, n, n_ext_dense=0, ext_identity=False, want_diag=True, check
     """In-place sweep over the stacked (n + r, ld) buffer ``e``.  Returns (diag(L), info tensor)."""
     dev = e.device
     ld = e.stride(0)
-    ws = torch.empty((max(_lib.potrf_workspace_bytes(n) // 4, 1),), device=dev, dtype=torch.float32)
+    ws_bytes = _lib.potrf_workspace_bytes(n, n_ext_dense)   # incl. the TMA scratch tail for large n
+    ws = torch.empty((max(ws_bytes // 4, 1),), device=dev, dtype=torch.float32)
     info = torch.empty((1,), device=dev, dtype=torch.int32)
     diag = torch.empty((n,), device=dev, dtype=torch.float32) if want_diag else None
-    call("potrf_ext", ptr(e), ld, n, n_ext_dense, int(ext_identity), ptr(diag), ptr(ws), ptr(info))
+    call("potrf_ext", ptr(e), ld, n, n_ext_dense, int(ext_identity), ptr(diag), ptr(ws), ws_bytes, ptr(info))
     if check:
         check_info(info)
     return diag, info
@@ -295,7 +296,11 @@ class _ExactGPLoss(torch.autograd.Function):
         alpha = torch.empty((n,), device=dev, dtype=torch.float32)
         call("gemv_rows", ptr(linv_t), ld, n, n, 1, ptr(z), ptr(alpha))
         dk = torch.empty((n, n), device=dev, dtype=torch.float32)
-        call("gp_nll_grad", ptr(linv_t), ld, n, ptr(diag), ptr(alpha), ptr(g), exact_logdet, ptr(dk), n)
+        ws_bytes = _lib.gp_nll_grad_workspace_bytes(n)
+        ws = torch.empty((ws_bytes // 4,), device=dev, dtype=torch.float32) if ws_bytes else None
+        call("gp_nll_grad", ptr(linv_t), ld, n, ptr(diag), ptr(alpha), ptr(g), exact_logdet, ptr(dk), n, ptr(ws),
+             ws_bytes)
+        del ws
         nx, ny, ns, nv, nl = ctx.needs_input_grad[:5]
         dx, _, dscale, dvar = gram_bwd_raw(kind, x, x, sc, var, dk, need_x=nx, need_y=False, need_scale=ns,
                                            need_var=nv, symmetric=True)

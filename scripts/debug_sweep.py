@@ -35,7 +35,7 @@ def main():
                          for _ in range(20)]
         ms = time_ms(f) / 20
         print("gemm m=%6d n=%5d k=%4d tb=%d : %8.1f us/launch  %7.2f TFLOP/s" % (m, n, k, tb, ms * 1e3, 2.0 * m * n * k / ms / 1e9))
-    for n in (1128, 4200):
+    for n in (1128, 4200, 8192, 16384):
         x = 0.1 * torch.randn(n, 128, device=DEV)
         sc, var = torch.zeros(128, device=DEV), torch.zeros((), device=DEV)
         k = ops.gram("rbf", x, None, sc, var, diag_add=0.05)

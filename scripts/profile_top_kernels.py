@@ -1,5 +1,5 @@
 """Launches the kernels the roofline claims are about, a few times each, for `ncu --set full`:
-  * tgemm_kernel<NT> as used by pinot_b200_gp_nll_grad at N = 4200 (bench.py's `roofline` kernel),
+  * tgemm_tma_kernel (TMA-fed tcgen05) as used by pinot_b200_gp_nll_grad at N = 4200 (bench.py's `roofline` kernel),
   * tgemm_kernel<NT> as one rank-64 trailing update of the Cholesky sweep (m = 4201, n = 4136),
   * mp_aggregate_kernel<4> on a 125k-molecule batch (HBM-sized), H = 128."""
 import os, sys, torch
@@ -13,8 +13,11 @@ diag = torch.rand(n, device=DEV) + 0.5
 alpha = torch.randn(n, device=DEV)
 g = torch.ones(1, device=DEV)
 dk = torch.empty(n, n, device=DEV)
+from pinot_b200 import _lib
+ws_bytes = _lib.gp_nll_grad_workspace_bytes(n)
+ws = torch.empty(max(ws_bytes // 4, 1), device=DEV)
 for _ in range(3):
-    call("gp_nll_grad", ptr(w), n, n, ptr(diag), ptr(alpha), ptr(g), 0, ptr(dk), n)
+    call("gp_nll_grad", ptr(w), n, n, ptr(diag), ptr(alpha), ptr(g), 0, ptr(dk), n, ptr(ws), ws_bytes)
 big = torch.randn(8500, 4200, device=DEV)
 for _ in range(3):
     call("sgemm", 0, 1, 4201, 4136, 64, -1.0, ptr(big), 4200, ptr(big), 4200, 1.0, ptr(big[:, 64:]), 4200)

@@ -34,10 +34,15 @@ def test_library_exports_every_declared_symbol():
 
 def test_loader_and_pure_host_entry_points():
     lib = _lib.load()
-    assert lib.pinot_b200_abi_version() == 1
+    assert lib.pinot_b200_abi_version() == 2
     assert _lib.potrf_workspace_bytes(0) == 0
     # two column blocks: L11 + L11^-T per block, plus the (256-byte rounded) flag array
     assert _lib.potrf_workspace_bytes(65) == 2 * 2 * 64 * 64 * 4 + 256
+    # the TMA scratch tail exists only where the sweep runs rank-512 outer updates (n >= 6144)
+    assert _lib.potrf_workspace_bytes(4200, 1) == _lib.potrf_workspace_bytes(4200)
+    assert _lib.potrf_workspace_bytes(8192, 1) - _lib.potrf_workspace_bytes(8192) == 2 * 8193 * 512 * 4
+    assert _lib.gp_nll_grad_workspace_bytes(100) == 0
+    assert _lib.gp_nll_grad_workspace_bytes(4200) == 2 * 4200 * 4200 * 4
     assert _lib.last_error() == "" or isinstance(_lib.last_error(), str)
 
 

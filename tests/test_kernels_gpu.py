@@ -157,6 +157,32 @@ def _kernel_params(kind, d, scale, variance):
     return sc, torch.tensor(variance)
 
 
+@pytest.mark.parametrize("m,n,k", [(300, 200, 100), (1024, 1152, 1030), (130, 72, 36), (128, 128, 2048)])
+def test_sgemm_nt_tma_matches_fp64_and_register_kernel(m, n, k):
+    """TMA-fed kernel (pre-split operands) = the same 3xTF32 arithmetic as pinot_b200_sgemm(0, 1, ...)."""
+    from pinot_b200 import _lib
+    from pinot_b200._lib import call, ptr
+    g = torch.Generator().manual_seed(m + n + k)
+    lda = ops._pad4(k)
+    a = torch.zeros(m, lda)
+    b = torch.zeros(n, lda)
+    a[:, :k] = torch.randn(m, k, generator=g)
+    b[:, :k] = torch.randn(n, k, generator=g)
+    c0 = torch.randn(m, n, generator=g)
+    want = 0.5 * (a[:, :k].double() @ b[:, :k].double().t()) - 2.0 * c0.double()
+    a, b = a.to(DEV), b.to(DEV)
+    nbytes = int(_lib.load().pinot_b200_sgemm_nt_tma_workspace_bytes(m, n, k))
+    ws = torch.empty(nbytes // 4, device=DEV)
+    got = c0.clone().to(DEV)
+    call("sgemm_nt_tma", m, n, k, 0.5, ptr(a), lda, ptr(b), lda, -2.0, ptr(got), n, ptr(ws), nbytes)
+    reg = c0.clone().to(DEV)
+    call("sgemm", 0, 1, m, n, k, 0.5, ptr(a), lda, ptr(b), lda, -2.0, ptr(reg), n)
+    assert rel_err(got, want) < 1e-5
+    assert rel_err(got, reg) < 1e-6
+    with pytest.raises(_lib.PinotB200Error, match="workspace too small"):
+        call("sgemm_nt_tma", m, n, k, 1.0, ptr(a), lda, ptr(b), lda, 0.0, ptr(got), n, ptr(ws), nbytes - 4)
+
+
 @pytest.mark.parametrize("kind", ["rbf", "matern52"])
 @pytest.mark.parametrize("n,n2,d", [(300, 300, 128), (131, 67, 32), (64, 200, 7), (1, 5, 3), (70, 70, 200)])
 def test_gram_forward(kind, n, n2, d):
@@ -258,6 +284,61 @@ def test_potrf_ext_identity_rows_give_inverse_transpose(n):
     assert rel_err(got, linv_t) < 1e-4
     assert torch.count_nonzero(torch.tril(got, -1)) == 0, "L^-T must stay exactly upper triangular"
     assert rel_err(e[n, :n], torch.linalg.solve_triangular(l, y[:, None], upper=False).flatten()) < 1e-4
+
+
+def test_potrf_two_level_sweep_with_and_without_tma_scratch():
+    """n >= 6144 runs rank-512 outer updates; given the scratch tail they go through the TMA-fed kernel.
+    Both routes must give the same factor, and the factor must reproduce the matrix."""
+    from pinot_b200 import _lib
+    from pinot_b200._lib import call, ptr
+    n, r = 6400, 3
+    g = torch.Generator().manual_seed(5)
+    a = torch.randn(n, 64, generator=g).to(DEV)
+    k = a @ a.t() / 64 + 2.0 * torch.eye(n, device=DEV)
+    ld = ops._pad4(n)
+    e0 = torch.zeros(2 * n + r, ld, device=DEV)
+    e0[:n, :n] = k
+    e0[n:n + r, :n] = torch.randn(r, n, generator=g).to(DEV)
+    e0[n + r:, :n].diagonal().fill_(1.0)
+    outs = []
+    for with_scratch in (False, True):
+        nbytes = _lib.potrf_workspace_bytes(n, r) if with_scratch else _lib.potrf_workspace_bytes(n)
+        ws = torch.empty(nbytes // 4, device=DEV)
+        e = e0.clone()
+        info = torch.zeros(1, dtype=torch.int32, device=DEV)
+        call("potrf_ext", ptr(e), ld, n, r, 1, None, ptr(ws), nbytes, ptr(info))
+        assert int(info.item()) == 0
+        outs.append(e)
+    assert _lib.potrf_workspace_bytes(n, r) > _lib.potrf_workspace_bytes(n)
+    assert rel_err(outs[1], outs[0]) < 1e-6
+    l = torch.tril(outs[1][:n, :n]).double()
+    assert rel_err(l @ l.t(), k.double()) < 1e-5
+    w = outs[1][n + r:, :n].double()                       # L^-T
+    assert rel_err(l.t() @ w, torch.eye(n, dtype=torch.float64, device=DEV)) < 1e-4
+
+
+def test_gp_nll_grad_tma_workspace_route_matches_register_route():
+    from pinot_b200 import _lib
+    from pinot_b200._lib import call, ptr
+    n = 1300
+    g = torch.Generator().manual_seed(11)
+    w = (torch.triu(torch.randn(n, n, generator=g)) * 0.05).to(DEV)
+    diag = (torch.rand(n, generator=g) + 0.5).to(DEV)
+    alpha = torch.randn(n, generator=g).to(DEV)
+    up = torch.full((1,), 0.7, device=DEV)
+    for exact in (0, 1):
+        wd = w.double() * (1.0 if exact else diag.double())
+        want = 0.7 * (0.5 * wd @ w.double().t() - 0.5 * torch.outer(alpha.double(), alpha.double()))
+        res = []
+        for nbytes in (0, _lib.gp_nll_grad_workspace_bytes(n)):
+            ws = torch.empty(nbytes // 4, device=DEV) if nbytes else None
+            dk = torch.full((n, n), float("nan"), device=DEV)
+            call("gp_nll_grad", ptr(w), n, n, ptr(diag), ptr(alpha), ptr(up), exact, ptr(dk), n, ptr(ws), nbytes)
+            res.append(dk)
+        assert _lib.gp_nll_grad_workspace_bytes(n) > 0
+        assert rel_err(res[0], want) < 1e-5 and rel_err(res[1], want) < 1e-5
+        assert rel_err(res[1], res[0]) < 1e-6
+        assert torch.equal(res[1], res[1].t())              # mirrored: exactly symmetric
 
 
 def test_potrf_reports_non_positive_definite_like_torch():

@@ -36,8 +36,9 @@ def _run(entry, e, ld, n, r):
     diag = torch.empty(n, device=DEV)
     info = torch.full((1,), -7, dtype=torch.int32, device=DEV)
     if entry == "potrf_ext":
-        ws = torch.empty(max(_lib.potrf_workspace_bytes(n) // 4, 1), device=DEV)
-        call(entry, ptr(e), ld, n, r, 1, ptr(diag), ptr(ws), ptr(info))
+        ws_bytes = _lib.potrf_workspace_bytes(n)
+        ws = torch.empty(max(ws_bytes // 4, 1), device=DEV)
+        call(entry, ptr(e), ld, n, r, 1, ptr(diag), ptr(ws), ws_bytes, ptr(info))
     else:
         call(entry, ptr(e), ld, n, r, 1, ptr(diag), ptr(info))
     torch.cuda.synchronize()
