@@ -289,14 +289,15 @@ def b200_main(args):
     n = n_mol
     grad_flop = n ** 3 / 3.0  # L^-T diag(L) L^-1, both factors triangular, symmetric result
     roofline = {
-        "kernel": "tgemm_kernel<NT> (tcgen05 3xTF32) in pinot_b200_gp_nll_grad: closed-form marginal-likelihood "
-                  "gradient 0.5 L^-T diag(L) L^-1 - 0.5 alpha alpha^T, N=%d" % n,
+        "kernel": "tgemm_tma_kernel (TMA-fed tcgen05 3xTF32, persistent) in pinot_b200_gp_nll_grad: closed-form "
+                  "marginal-likelihood gradient 0.5 L^-T diag(L) L^-1 - 0.5 alpha alpha^T, N=%d; the timed span "
+                  "is the whole C-ABI call (hi/lo split pass + GEMM)" % n,
         "bound": "tensor", "achieved": grad_flop / (grad_ms * 1e-3) / 1e12 if grad_ms else None,
         "peak": tf_peak, "unit": "TFLOP/s", "peak_source": peak_src + ", bf16 sustained",
         "traffic": None,
         "note": "algorithmic flops N^3/3 (triangular x triangular, symmetric output); the fp32-parity path "
                 "issues 3 TF32 MMAs per product, so the tensor pipe executes 3x these flops at the TF32 rate "
-                "(half the bf16 peak used as denominator)",
+                "(half the bf16 peak used as denominator): frac = 1/6 would be a saturated TF32 pipe",
     }
     if roofline["achieved"] is not None:
         roofline["frac"] = roofline["achieved"] / tf_peak

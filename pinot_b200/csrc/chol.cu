@@ -332,8 +332,8 @@ int64_t pinot_b200_potrf_tma_scratch_bytes(int64_t n, int64_t n_ext_dense) {
     if (n < 0 || n_ext_dense < 0) return -1;
     const int64_t W = outer_block_width(n);
     if (W <= NB || !pb::gemm_tma_enabled()) return 0;   // single-level sweep: no rank-W updates
-    // hi / lo copies of one (n + n_ext_dense) x W panel
-    return (int64_t)sizeof(float) * 2 * (n + n_ext_dense) * W;
+    // tile counter + hi / lo copies of one (n + n_ext_dense) x W panel
+    return (int64_t)sizeof(float) * (pb::TMA_COUNTER_FLOATS + 2 * (n + n_ext_dense) * W);
 }
 
 int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, int ext_identity,
@@ -434,7 +434,7 @@ int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, i
             const int64_t row_end = active_rows_end(J1);
             const int64_t rows = row_end - J1, K = J1 - J0, ldk = (K + 3) / 4 * 4;
             PB_REQUIRE(rows <= n + n_ext_dense, "potrf_ext: internal error (panel of %lld rows)", (long long)rows);
-            float* hi = tma_scratch;
+            float* hi = tma_scratch + pb::TMA_COUNTER_FLOATS;
             float* lo = hi + rows * ldk;
             int rc = pb::tma_split_operand(e + J1 * ld + J0, ld, rows, K, hi, lo, nullptr, 0, 0, stream);
             if (rc) return rc;
@@ -452,7 +452,8 @@ int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, i
             p.M = (int)(rows - o); p.N = (int)(n - J1 - o); p.K = (int)K;
             p.C = e + (J1 + o) * ld + (J1 + o); p.ldc = ld;
             p.alpha = -1.f; p.beta = 1.f; p.lower = 1; p.splitk = 1; p.vecC = 1;
-            rc = pb::launch_gemm_tma_presplit(p, hi + o * ldk, lo + o * ldk, hi + o * ldk, lo + o * ldk, stream);
+            rc = pb::launch_gemm_tma_presplit(p, hi + o * ldk, lo + o * ldk, hi + o * ldk, lo + o * ldk,
+                                              reinterpret_cast<int*>(tma_scratch), stream);
             if (rc) return rc;
         } else if (J1 < n) {
             const int64_t row_end = active_rows_end(J1);
@@ -607,7 +608,8 @@ int pinot_b200_gemv_rows(const float* m, int64_t ld, int64_t rows, int64_t cols,
 int64_t pinot_b200_gp_nll_grad_workspace_bytes(int64_t n) {
     if (n < 0) return -1;
     if (n < TMA_MIN_N || !pb::gemm_tma_enabled()) return 0;
-    return (int64_t)sizeof(float) * 2 * n * ((n + 3) / 4 * 4);   // hi / lo copies of L^{-T} diag(L)^{1/2}
+    // tile counter + hi / lo copies of L^{-T} diag(L)^{1/2}
+    return (int64_t)sizeof(float) * (pb::TMA_COUNTER_FLOATS + 2 * n * ((n + 3) / 4 * 4));
 }
 
 int pinot_b200_gp_nll_grad(const float* linv_t, int64_t ld, int64_t n, const float* diag_l,
@@ -626,7 +628,7 @@ int pinot_b200_gp_nll_grad(const float* linv_t, int64_t ld, int64_t n, const flo
         if (need > 0 && workspace && workspace_bytes >= need && ld % 4 == 0 && ld >= n4 && lddk % 4 == 0 &&
             pb::aligned16(linv_t) && pb::aligned16(dk) && pb::aligned16(workspace) &&
             (exact_logdet || pb::aligned16(diag_l))) {
-            float* hi = static_cast<float*>(workspace);
+            float* hi = static_cast<float*>(workspace) + pb::TMA_COUNTER_FLOATS;
             float* lo = hi + n * n4;
             int rc = pb::tma_split_operand(linv_t, ld, n, n, hi, lo, diag_l, exact_logdet ? 0 : 2, 1, stream);
             if (rc) return rc;
@@ -636,7 +638,7 @@ int pinot_b200_gp_nll_grad(const float* linv_t, int64_t ld, int64_t n, const flo
             p.alpha = 0.5f; p.beta = 0.f; p.alpha_dev = upstream;
             p.r1u = alpha; p.r1v = alpha; p.r1coef = -0.5f;
             p.lower = 1; p.mirror = 1; p.ktri = 1; p.splitk = 1; p.vecC = 1;
-            return pb::launch_gemm_tma_presplit(p, hi, lo, hi, lo, stream);
+            return pb::launch_gemm_tma_presplit(p, hi, lo, hi, lo, static_cast<int*>(workspace), stream);
         }
     }
     pb::GemmParams g;

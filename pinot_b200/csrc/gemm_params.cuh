@@ -32,7 +32,9 @@ bool gemm_tma_enabled();   // tensor-core GEMMs selected and PINOT_B200_TMA != 0
 // 1 = columns * colscale, 2 = columns * sqrt(colscale); tri: upper-triangular operand of a ktri product
 int tma_split_operand(const float* x, int64_t ldx, int64_t rows, int64_t K, float* hi, float* lo, const float* colscale,
                       int scale_mode, int tri, cudaStream_t stream);
+// tile_counter: one int of device scratch for the kernel's dynamic tile queue (zeroed here, on the stream)
 int launch_gemm_tma_presplit(const KParams& p, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo,
-                             cudaStream_t stream);
+                             int* tile_counter, cudaStream_t stream);
+constexpr int64_t TMA_COUNTER_FLOATS = 64;   // callers reserve 256 bytes for that counter
 
 }  // namespace pb

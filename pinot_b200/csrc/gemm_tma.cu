@@ -31,6 +31,7 @@ constexpr int SMEM_BYTES = NSTAGE * STAGE_BYTES + EPI_BYTES + 1024;
 constexpr int NTHREADS = 192;                      // producer, MMA, 4 epilogue warps
 constexpr int KCHUNK = 512;
 constexpr int STAGES_PER_CHUNK = KCHUNK / BK;
+constexpr int NSCHED = 4;                          // depth of the tile hand-off ring
 
 __device__ __forceinline__ uint32_t s32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -84,22 +85,65 @@ __device__ __forceinline__ void mma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(s32(bar)) : "memory");
 }
 
+// Live tiles in dispatch order.  Without `lower` the gm x gn rectangle row by row; with it only tiles on or
+// below the diagonal (row i has min(i + 1, gn) of them), still row by row -- for a ktri product that is
+// longest-K first.
+struct TileGrid {
+    int gm, gn, lower;
+    __host__ __device__ int count() const {
+        if (!lower) return gm * gn;
+        const int t = gm < gn ? gm : gn;
+        return t * (t + 1) / 2 + (gm > gn ? (gm - gn) * gn : 0);
+    }
+    __device__ void locate(int t, int& i, int& j) const {
+        if (!lower) { i = t / gn; j = t - i * gn; return; }
+        const int tri = gn * (gn + 1) / 2;
+        if (t < tri) {
+            i = (int)((sqrtf(8.f * (float)t + 1.f) - 1.f) * 0.5f);
+            while ((i + 1) * (i + 2) / 2 <= t) ++i;
+            while (i * (i + 1) / 2 > t) --i;
+            j = t - i * (i + 1) / 2;
+        } else {
+            const int r = t - tri;
+            i = gn + r / gn;
+            j = r - (r / gn) * gn;
+        }
+    }
+};
+
+struct TileWork {
+    int m0, n0, kb, num_k, num_chunks;
+};
+__device__ __forceinline__ TileWork tile_work(const KParams& p, const TileGrid& tg, int t) {
+    int i, j;
+    tg.locate(t, i, j);
+    TileWork w;
+    w.m0 = i * BM;
+    w.n0 = j * BN;
+    w.kb = p.ktri ? (w.m0 / BK) * BK : 0;
+    w.num_k = (p.K > w.kb) ? (p.K - w.kb + BK - 1) / BK : 0;
+    w.num_chunks = (w.num_k + STAGES_PER_CHUNK - 1) / STAGES_PER_CHUNK;   // 0 when there is nothing to multiply
+    return w;
+}
+
+// Persistent with a dynamic tile queue: the producer thread draws the next live tile from a global counter
+// (zeroed by the host before the launch) and hands it to the MMA and epilogue warps through a 4-slot ring in
+// shared memory -- a ktri product has tiles of very different length, which a static assignment balances
+// badly.  The three roles keep their own running counters (stage ring position, accumulator-set use count),
+// so the drain of one tile's last K-chunk overlaps the MMAs of the next tile's first one.
 template <int EPI>
 __global__ void __launch_bounds__(NTHREADS, 1)
-tgemm_tma_kernel(const KParams p, const __grid_constant__ CUtensorMap map_ah, const __grid_constant__ CUtensorMap map_al,
-                 const __grid_constant__ CUtensorMap map_bh, const __grid_constant__ CUtensorMap map_bl) {
+tgemm_tma_kernel(const KParams p, const TileGrid tg, int* __restrict__ tile_counter,
+                 const __grid_constant__ CUtensorMap map_ah,
+                 const __grid_constant__ CUtensorMap map_al, const __grid_constant__ CUtensorMap map_bh,
+                 const __grid_constant__ CUtensorMap map_bl) {
     extern __shared__ __align__(1024) uint8_t dyn_smem[];
     __shared__ __align__(8) uint64_t full_bar[NSTAGE], empty_bar[NSTAGE], acc_full[2], acc_empty[2];
+    __shared__ __align__(8) uint64_t sched_full[NSCHED], sched_empty[NSCHED];
+    __shared__ int sched_tile[NSCHED];
     __shared__ uint32_t tmem_base_holder;
 
-    const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
-    if (p.lower && n0 > m0 + BM - 1) return;
-    int kb = 0;
-    const int ke = p.K;
-    if (p.ktri) kb = (m0 / BK) * BK;
-    const int num_k = (ke > kb) ? (ke - kb + BK - 1) / BK : 0;
-    const int num_chunks = num_k > 0 ? (num_k + STAGES_PER_CHUNK - 1) / STAGES_PER_CHUNK : 1;
-
+    const int ntiles = tg.count();
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dyn_smem) + 1023) & ~(uintptr_t)1023);
     float* epi_smem = reinterpret_cast<float*>(smem + NSTAGE * STAGE_BYTES);
@@ -112,6 +156,10 @@ tgemm_tma_kernel(const KParams p, const __grid_constant__ CUtensorMap map_ah, co
         for (int s = 0; s < 2; ++s) {
             mbar_init(&acc_full[s], 1);
             mbar_init(&acc_empty[s], 128);
+        }
+        for (int s = 0; s < NSCHED; ++s) {
+            mbar_init(&sched_full[s], 1);
+            mbar_init(&sched_empty[s], 129);   // the MMA thread and the 128 epilogue threads
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_ah) : "memory");
@@ -133,46 +181,65 @@ tgemm_tma_kernel(const KParams p, const __grid_constant__ CUtensorMap map_ah, co
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (lane == 0) {
-            for (int kt = 0; kt < num_k; ++kt) {
-                const int s = kt % NSTAGE;
-                if (kt >= NSTAGE) mbar_wait(&empty_bar[s], (uint32_t)((kt / NSTAGE - 1) & 1));
-                uint8_t* st = smem + s * STAGE_BYTES;
-                mbar_expect_tx(&full_bar[s], STAGE_BYTES);
-                const int kc = kb + kt * BK;
-                tma_load_2d(st, &map_ah, kc, m0, &full_bar[s]);
-                tma_load_2d(st + TILE_BYTES, &map_al, kc, m0, &full_bar[s]);
-                tma_load_2d(st + 2 * TILE_BYTES, &map_bh, kc, n0, &full_bar[s]);
-                tma_load_2d(st + 3 * TILE_BYTES, &map_bl, kc, n0, &full_bar[s]);
+            uint32_t it = 0;   // stages issued so far
+            for (uint32_t ns = 0;; ++ns) {
+                const uint32_t slot = ns % NSCHED;
+                if (ns >= NSCHED) mbar_wait(&sched_empty[slot], (ns / NSCHED - 1) & 1);
+                const int t = atomicAdd(tile_counter, 1);
+                *reinterpret_cast<volatile int*>(&sched_tile[slot]) = t;
+                mbar_arrive(&sched_full[slot]);
+                if (t >= ntiles) break;
+                const TileWork w = tile_work(p, tg, t);
+                for (int kt = 0; kt < w.num_k; ++kt, ++it) {
+                    const uint32_t s = it % NSTAGE;
+                    if (it >= NSTAGE) mbar_wait(&empty_bar[s], (it / NSTAGE - 1) & 1);
+                    uint8_t* st = smem + s * STAGE_BYTES;
+                    mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                    const int kc = w.kb + kt * BK;
+                    tma_load_2d(st, &map_ah, kc, w.m0, &full_bar[s]);
+                    tma_load_2d(st + TILE_BYTES, &map_al, kc, w.m0, &full_bar[s]);
+                    tma_load_2d(st + 2 * TILE_BYTES, &map_bh, kc, w.n0, &full_bar[s]);
+                    tma_load_2d(st + 3 * TILE_BYTES, &map_bl, kc, w.n0, &full_bar[s]);
+                }
             }
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
         if (lane == 0) {
             const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-            for (int chunk = 0; chunk < num_chunks; ++chunk) {
-                const int set = chunk & 1;
-                if (chunk >= 2) mbar_wait(&acc_empty[set], (uint32_t)((chunk / 2 - 1) & 1));
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t acc_hi = tmem_d + (uint32_t)(set * 256), acc_x = acc_hi + 128u;
-                const int kt_beg = chunk * STAGES_PER_CHUNK, kt_end = min(num_k, kt_beg + STAGES_PER_CHUNK);
-                for (int kt = kt_beg; kt < kt_end; ++kt) {
-                    const int s = kt % NSTAGE;
-                    mbar_wait(&full_bar[s], (uint32_t)((kt / NSTAGE) & 1));
+            uint32_t it = 0, gc = 0;   // stages / accumulator sets consumed so far
+            for (uint32_t ns = 0;; ++ns) {
+                const uint32_t slot = ns % NSCHED;
+                mbar_wait(&sched_full[slot], (ns / NSCHED) & 1);
+                const int t = *reinterpret_cast<volatile int*>(&sched_tile[slot]);
+                mbar_arrive(&sched_empty[slot]);
+                if (t >= ntiles) break;
+                const TileWork w = tile_work(p, tg, t);
+                for (int chunk = 0; chunk < w.num_chunks; ++chunk, ++gc) {
+                    const uint32_t set = gc & 1;
+                    if (gc >= 2) mbar_wait(&acc_empty[set], (gc / 2 - 1) & 1);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    const uint32_t sb = s32(smem + s * STAGE_BYTES);
-                    const uint64_t d_ah = sw128_desc(sb), d_al = sw128_desc(sb + TILE_BYTES);
-                    const uint64_t d_bh = sw128_desc(sb + 2 * TILE_BYTES), d_bl = sw128_desc(sb + 3 * TILE_BYTES);
+                    const uint32_t acc_hi = tmem_d + set * 256u, acc_x = acc_hi + 128u;
+                    const int kt_beg = chunk * STAGES_PER_CHUNK, kt_end = min(w.num_k, kt_beg + STAGES_PER_CHUNK);
+                    for (int kt = kt_beg; kt < kt_end; ++kt, ++it) {
+                        const uint32_t s = it % NSTAGE;
+                        mbar_wait(&full_bar[s], (it / NSTAGE) & 1);
+                        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                        const uint32_t sb = s32(smem + s * STAGE_BYTES);
+                        const uint64_t d_ah = sw128_desc(sb), d_al = sw128_desc(sb + TILE_BYTES);
+                        const uint64_t d_bh = sw128_desc(sb + 2 * TILE_BYTES), d_bl = sw128_desc(sb + 3 * TILE_BYTES);
 #pragma unroll
-                    for (int k8 = 0; k8 < BK / 8; ++k8) {
-                        const uint64_t adv = (uint64_t)((k8 * 32) >> 4);   // +32 bytes inside the swizzle atom
-                        const uint32_t acc = (kt > kt_beg || k8 > 0) ? 1u : 0u;
-                        mma_tf32(acc_x, d_al + adv, d_bh + adv, idesc, acc);
-                        mma_tf32(acc_x, d_ah + adv, d_bl + adv, idesc, 1u);
-                        mma_tf32(acc_hi, d_ah + adv, d_bh + adv, idesc, acc);
+                        for (int k8 = 0; k8 < BK / 8; ++k8) {
+                            const uint64_t adv = (uint64_t)((k8 * 32) >> 4);   // +32 bytes inside the swizzle atom
+                            const uint32_t acc = (kt > kt_beg || k8 > 0) ? 1u : 0u;
+                            mma_tf32(acc_x, d_al + adv, d_bh + adv, idesc, acc);
+                            mma_tf32(acc_x, d_ah + adv, d_bl + adv, idesc, 1u);
+                            mma_tf32(acc_hi, d_ah + adv, d_bh + adv, idesc, acc);
+                        }
+                        mma_commit(&empty_bar[s]);     // stage free once these MMAs have read it
                     }
-                    mma_commit(&empty_bar[s]);     // stage free once these MMAs have read it
+                    mma_commit(&acc_full[set]);        // accumulators of this chunk complete
                 }
-                mma_commit(&acc_full[set]);        // accumulators of this chunk complete
             }
         }
     } else {
@@ -185,64 +252,81 @@ tgemm_tma_kernel(const KParams p, const __grid_constant__ CUtensorMap map_ah, co
         }
         const int q = warp & 3;                       // TMEM lane quadrant this warp may access
         float* tile = epi_smem + (warp - 2) * (32 * EPI_LD);
-        for (int chunk = 0; chunk < num_chunks; ++chunk) {
-            const int set = chunk & 1;
-            const bool last_chunk = (chunk == num_chunks - 1);
-            const float beta = (chunk == 0) ? p.beta : 1.f;
-            if (num_k > 0) mbar_wait(&acc_full[set], (uint32_t)((chunk / 2) & 1));
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        uint32_t gc = 0;
+        for (uint32_t ns = 0;; ++ns) {
+            const uint32_t slot = ns % NSCHED;
+            mbar_wait(&sched_full[slot], (ns / NSCHED) & 1);
+            const int t = *reinterpret_cast<volatile int*>(&sched_tile[slot]);
+            mbar_arrive(&sched_empty[slot]);
+            if (t >= ntiles) break;
+            const TileWork w = tile_work(p, tg, t);
+            const int passes = w.num_chunks > 0 ? w.num_chunks : 1;   // an empty product still applies beta / bias
+            for (int chunk = 0; chunk < passes; ++chunk) {
+                const bool have_acc = w.num_chunks > 0;
+                const uint32_t set = gc & 1;
+                const bool last_chunk = (chunk == passes - 1);
+                const float beta = (chunk == 0) ? p.beta : 1.f;
+                if (have_acc) {
+                    mbar_wait(&acc_full[set], (gc / 2) & 1);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                }
 #pragma unroll 1
-            for (int c0 = 0; c0 < BN; c0 += 32) {
-                uint32_t v[32], w[32];
-                if (num_k > 0) {
-                    const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(set * 256 + c0);
-                    asm volatile(
-                        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-                        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-                        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
-                        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
-                          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
-                          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-                        : "r"(taddr)
-                        : "memory");
-                    asm volatile(
-                        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-                        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-                        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
-                        : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]),
-                          "=r"(w[8]), "=r"(w[9]), "=r"(w[10]), "=r"(w[11]), "=r"(w[12]), "=r"(w[13]), "=r"(w[14]), "=r"(w[15]),
-                          "=r"(w[16]), "=r"(w[17]), "=r"(w[18]), "=r"(w[19]), "=r"(w[20]), "=r"(w[21]), "=r"(w[22]), "=r"(w[23]),
-                          "=r"(w[24]), "=r"(w[25]), "=r"(w[26]), "=r"(w[27]), "=r"(w[28]), "=r"(w[29]), "=r"(w[30]), "=r"(w[31])
-                        : "r"(taddr + 128u)
-                        : "memory");
-                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                } else {
+                for (int c0 = 0; c0 < BN; c0 += 32) {
+                    uint32_t v[32], x[32];
+                    if (have_acc) {
+                        const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + set * 256u + (uint32_t)c0;
+                        asm volatile(
+                            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                            "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+                            : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                              "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                              "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                              "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                            : "r"(taddr)
+                            : "memory");
+                        asm volatile(
+                            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                            "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+                            : "=r"(x[0]), "=r"(x[1]), "=r"(x[2]), "=r"(x[3]), "=r"(x[4]), "=r"(x[5]), "=r"(x[6]), "=r"(x[7]),
+                              "=r"(x[8]), "=r"(x[9]), "=r"(x[10]), "=r"(x[11]), "=r"(x[12]), "=r"(x[13]), "=r"(x[14]), "=r"(x[15]),
+                              "=r"(x[16]), "=r"(x[17]), "=r"(x[18]), "=r"(x[19]), "=r"(x[20]), "=r"(x[21]), "=r"(x[22]), "=r"(x[23]),
+                              "=r"(x[24]), "=r"(x[25]), "=r"(x[26]), "=r"(x[27]), "=r"(x[28]), "=r"(x[29]), "=r"(x[30]), "=r"(x[31])
+                            : "r"(taddr + 128u)
+                            : "memory");
+                        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    } else {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) { v[j] = 0u; w[j] = 0u; }
-                }
+                        for (int jj = 0; jj < 32; ++jj) { v[jj] = 0u; x[jj] = 0u; }
+                    }
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    float4 t;
-                    t.x = __uint_as_float(v[4 * i + 0]) + __uint_as_float(w[4 * i + 0]);
-                    t.y = __uint_as_float(v[4 * i + 1]) + __uint_as_float(w[4 * i + 1]);
-                    t.z = __uint_as_float(v[4 * i + 2]) + __uint_as_float(w[4 * i + 2]);
-                    t.w = __uint_as_float(v[4 * i + 3]) + __uint_as_float(w[4 * i + 3]);
-                    *reinterpret_cast<float4*>(tile + lane * EPI_LD + 4 * i) = t;
+                    for (int i = 0; i < 8; ++i) {
+                        float4 o;
+                        o.x = __uint_as_float(v[4 * i + 0]) + __uint_as_float(x[4 * i + 0]);
+                        o.y = __uint_as_float(v[4 * i + 1]) + __uint_as_float(x[4 * i + 1]);
+                        o.z = __uint_as_float(v[4 * i + 2]) + __uint_as_float(x[4 * i + 2]);
+                        o.w = __uint_as_float(v[4 * i + 3]) + __uint_as_float(x[4 * i + 3]);
+                        *reinterpret_cast<float4*>(tile + lane * EPI_LD + 4 * i) = o;
+                    }
+                    __syncwarp();
+                    epilogue_rows<EPI>(p, tile, alpha, beta, r1c, last_chunk, w.m0, w.n0, q, c0, lane);
+                    __syncwarp();
                 }
-                __syncwarp();
-                epilogue_rows<EPI>(p, tile, alpha, beta, r1c, last_chunk, m0, n0, q, c0, lane);
-                __syncwarp();
+                if (have_acc) {
+                    // this accumulator set may be overwritten by the chunk after next
+                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                    mbar_arrive(&acc_empty[set]);
+                    ++gc;
+                }
             }
-            // this accumulator set may be overwritten by chunk + 2
-            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-            mbar_arrive(&acc_empty[set]);
         }
     }
 
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (warp == 1) {
+        __syncwarp();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(512u) : "memory");
     }
 }
@@ -275,6 +359,16 @@ split_tf32_kernel(const float* __restrict__ x, int64_t ldx, float* __restrict__ 
 #undef PB_SPLIT
     *reinterpret_cast<float4*>(hi + r * ldo + c) = h;
     *reinterpret_cast<float4*>(lo + r * ldo + c) = l;
+}
+
+int num_sms() {
+    static const int n = [] {
+        int dev = 0, v = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) return 148;
+        return v;
+    }();
+    return n;
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -310,9 +404,10 @@ int make_map(CUtensorMap* map, const float* base, int64_t rows, int64_t cols, in
 
 }  // namespace
 
+// hi / lo copies plus 64 floats (256 bytes) for the tile counter, which sits FIRST
 int64_t gemm_tma_scratch_floats(int64_t M, int64_t N, int64_t K, bool same_operand) {
     const int64_t ldk = (K + 3) / 4 * 4;
-    return 2 * M * ldk + (same_operand ? 0 : 2 * N * ldk);
+    return TMA_COUNTER_FLOATS + 2 * M * ldk + (same_operand ? 0 : 2 * N * ldk);
 }
 
 bool gemm_tma_enabled() {
@@ -337,7 +432,7 @@ int tma_split_operand(const float* x, int64_t ldx, int64_t rows, int64_t K, floa
 
 // C (M x N) = alpha A B^T (+ ...) from pre-split operands: a_* (M x K), b_* (N x K), leading dimension ceil4(K).
 int launch_gemm_tma_presplit(const KParams& p, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo,
-                             cudaStream_t stream) {
+                             int* tile_counter, cudaStream_t stream) {
     const int64_t M = p.M, N = p.N, K = p.K;
     const int64_t ldk = (K + 3) / 4 * 4;
     PB_REQUIRE(p.vecC && p.ldc % 4 == 0 && aligned16(p.C), "gemm (TMA): C must be 16-byte aligned with ldc % 4 == 0");
@@ -349,11 +444,15 @@ int launch_gemm_tma_presplit(const KParams& p, const float* a_hi, const float* a
     if ((rc = make_map(&mal, a_lo, M, K, ldk))) return rc;
     if ((rc = make_map(&mbh, b_hi, N, K, ldk))) return rc;
     if ((rc = make_map(&mbl, b_lo, N, K, ldk))) return rc;
-    dim3 grid((unsigned)ceil_div(N, BN), (unsigned)ceil_div(M, BM), 1);
-    PB_REQUIRE(grid.y <= 65535, "gemm (TMA): M too large for one launch (%d rows)", p.M);
+    TileGrid tg;
+    tg.gm = (int)ceil_div(M, BM); tg.gn = (int)ceil_div(N, BN); tg.lower = p.lower;
+    const int ntiles = tg.count();
+    const unsigned grid = (unsigned)(ntiles < num_sms() ? ntiles : num_sms());
+    PB_REQUIRE(tile_counter != nullptr, "gemm (TMA): tile counter missing");
+    PB_CUDA(cudaMemsetAsync(tile_counter, 0, sizeof(int), stream));
     auto launch = [&](auto kern) -> int {
         PB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        kern<<<grid, NTHREADS, SMEM_BYTES, stream>>>(p, mah, mal, mbh, mbl);
+        kern<<<grid, NTHREADS, SMEM_BYTES, stream>>>(p, tg, tile_counter, mah, mal, mbh, mbl);
         return check_launch("gemm (tcgen05 + TMA)");
     };
     if (p.r1u || p.mirror) return launch(tgemm_tma_kernel<2>);
@@ -364,7 +463,7 @@ int launch_gemm_tma_presplit(const KParams& p, const float* a_hi, const float* a
 int launch_gemm_tma(const KParams& p, float* scratch, bool same_operand, cudaStream_t stream) {
     const int64_t M = p.M, N = p.N, K = p.K;
     const int64_t ldk = (K + 3) / 4 * 4;
-    float* a_hi = scratch;
+    float* a_hi = scratch + TMA_COUNTER_FLOATS;
     float* a_lo = a_hi + M * ldk;
     float* b_hi = same_operand ? a_hi : a_lo + M * ldk;
     float* b_lo = same_operand ? a_lo : b_hi + N * ldk;
@@ -374,7 +473,7 @@ int launch_gemm_tma(const KParams& p, float* scratch, bool same_operand, cudaStr
         rc = tma_split_operand(p.B, p.ldb, N, K, b_hi, b_lo, nullptr, 0, 0, stream);
         if (rc) return rc;
     }
-    return launch_gemm_tma_presplit(p, a_hi, a_lo, b_hi, b_lo, stream);
+    return launch_gemm_tma_presplit(p, a_hi, a_lo, b_hi, b_lo, reinterpret_cast<int*>(scratch), stream);
 }
 
 }  // namespace pb
