@@ -110,6 +110,19 @@ PINOT_B200_API int pinot_b200_sgemm_nt_tma(int64_t M, int64_t N, int64_t K, floa
                             const float* B, int64_t ldb, float beta, float* C, int64_t ldc, void* workspace,
                             int64_t workspace_bytes, cudaStream_t stream);
 
+/* The two halves of pinot_b200_sgemm_nt_tma for callers that reuse one operand in several products
+ * (the panel of a blocked / sharded Cholesky: split once, then one update per column block).
+ * tf32_split: hi = tf32(v), lo = tf32(v - hi), v = x * f(colscale[col]) with f = 1 (scale_mode 0),
+ * identity (1) or sqrt (2); hi / lo are rows x ceil4(K) arrays (leading dimension ceil4(K)).
+ * sgemm_nt_presplit: C (M x N) = alpha A B^T + beta C from such arrays; lower != 0 computes only
+ * elements with column <= row; tile_counter is one int of device scratch (set by the call).
+ * No direct counterpart in the reference (the `@` products of gaussian_process_regressor.py:212-218). */
+PINOT_B200_API int pinot_b200_tf32_split(const float* x, int64_t ldx, int64_t rows, int64_t K, const float* colscale,
+                          int scale_mode, float* hi, float* lo, cudaStream_t stream);
+PINOT_B200_API int pinot_b200_sgemm_nt_presplit(int64_t M, int64_t N, int64_t K, float alpha, const float* a_hi,
+                                 const float* a_lo, const float* b_hi, const float* b_lo, float beta, float* C,
+                                 int64_t ldc, int lower, int* tile_counter, cudaStream_t stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Kernel (3): Gram matrix.  kind 0 = RBF (pinot/regressors/kernels/rbf.py:31-55: exp(variance) *
  * exp(-0.5 * ||(x - x') * exp(scale)||_2)), kind 1 = Matern-5/2 (pinot/regressors/kernels/matern.py:30-63).
@@ -125,6 +138,9 @@ PINOT_B200_API int pinot_b200_gram_fwd(int kind, const float* x, const float* y,
 /* Backward of the Gram matrix given dk = dLoss/dK (n x n2).  Outputs (any may be NULL, all are
  * overwritten): dx (n x d), dy (n2 x d), dscale (scale_len), dvariance (1).  symmetric = 1 promises
  * x == y and dk == dk^T: only the row-side pass runs and the caller doubles dx and dscale.
+ * symmetric = 2: x is a ROW BLOCK of y and dk the same rows of a symmetric matrix (row-sharded GP):
+ * row-side pass only; doubled dx is the full gradient of those rows, doubled dscale sums to the full
+ * gradient over all row blocks.
  * Replaces autograd through torch.norm / exp at kernels/rbf.py:31-53 (sub-gradient 0 at d = 0).
  * Limit: d <= 256. */
 PINOT_B200_API int pinot_b200_gram_bwd(int kind, const float* x, const float* y, const float* scale,

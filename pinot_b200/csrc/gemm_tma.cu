@@ -505,5 +505,29 @@ int pinot_b200_sgemm_nt_tma(int64_t M, int64_t N, int64_t K, float alpha, const 
     return pb::launch_gemm_tma(p, static_cast<float*>(workspace), false, stream);
 }
 
-}  // extern "C"
+int pinot_b200_tf32_split(const float* x, int64_t ldx, int64_t rows, int64_t K, const float* colscale, int scale_mode,
+                          float* hi, float* lo, cudaStream_t stream) {
+    PB_REQUIRE(rows >= 0 && K > 0 && rows < (1ll << 31) && K < (1ll << 31), "tf32_split: invalid sizes");
+    PB_REQUIRE(scale_mode >= 0 && scale_mode <= 2, "tf32_split: scale_mode must be 0, 1 or 2");
+    if (rows == 0) return pb::PB_OK;
+    PB_REQUIRE(x && hi && lo, "tf32_split: null pointer");
+    return pb::tma_split_operand(x, ldx, rows, K, hi, lo, colscale, scale_mode, 0, stream);
+}
 
+int pinot_b200_sgemm_nt_presplit(int64_t M, int64_t N, int64_t K, float alpha, const float* a_hi, const float* a_lo,
+                                 const float* b_hi, const float* b_lo, float beta, float* C, int64_t ldc, int lower,
+                                 int* tile_counter, cudaStream_t stream) {
+    PB_REQUIRE(M > 0 && N > 0 && K > 0, "sgemm_nt_presplit: empty product");
+    PB_REQUIRE(M < (1ll << 31) && N < (1ll << 31) && K < (1ll << 31), "sgemm_nt_presplit: size exceeds int32");
+    PB_REQUIRE(a_hi && a_lo && b_hi && b_lo && C && tile_counter, "sgemm_nt_presplit: null pointer");
+    auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+    PB_REQUIRE(al16(a_hi) && al16(a_lo) && al16(b_hi) && al16(b_lo) && al16(C) && ldc % 4 == 0 && ldc >= N,
+               "sgemm_nt_presplit: operands must be 16-byte aligned with ldc a multiple of 4");
+    pb::KParams p{};
+    p.M = (int)M; p.N = (int)N; p.K = (int)K;
+    p.C = C; p.ldc = ldc;
+    p.alpha = alpha; p.beta = beta; p.lower = lower ? 1 : 0; p.splitk = 1; p.vecC = 1;
+    return pb::launch_gemm_tma_presplit(p, a_hi, a_lo, b_hi, b_lo, tile_counter, stream);
+}
+
+}  // extern "C"

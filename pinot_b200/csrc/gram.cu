@@ -329,7 +329,8 @@ int pinot_b200_gram_bwd(int kind, const float* x, const float* y, const float* s
     PB_REQUIRE(n >= 0 && n2 >= 0 && d > 0, "gram_bwd: invalid sizes");
     PB_REQUIRE(d <= 256, "gram_bwd: feature dimension %lld exceeds the supported maximum of 256", (long long)d);
     PB_REQUIRE(scale_len == 1 || scale_len == d, "gram_bwd: scale must have 1 or d entries");
-    PB_REQUIRE(!symmetric || (n == n2 && x == y), "gram_bwd: symmetric mode needs x == y");
+    PB_REQUIRE(symmetric >= 0 && symmetric <= 2, "gram_bwd: symmetric must be 0, 1 or 2");
+    PB_REQUIRE(symmetric != 1 || (n == n2 && x == y), "gram_bwd: symmetric mode needs x == y");
     if (dx) PB_CUDA(cudaMemsetAsync(dx, 0, sizeof(float) * n * d, stream));
     if (dy) PB_CUDA(cudaMemsetAsync(dy, 0, sizeof(float) * n2 * d, stream));
     if (dscale) PB_CUDA(cudaMemsetAsync(dscale, 0, sizeof(float) * scale_len, stream));
@@ -350,8 +351,10 @@ int pinot_b200_gram_bwd(int kind, const float* x, const float* y, const float* s
     if (rc) return rc;
     // column-side pass (roles swapped, dK read transposed): dy and the column half of dscale.
     // In symmetric mode the caller promises x == y and dK == dK^T, so the column pass would
-    // reproduce the row pass: it is skipped and the Python layer doubles dx / dscale.
-    if (!symmetric && (dy || dscale)) {
+    // reproduce the row pass: it is skipped and the Python layer doubles dx / dscale.  Mode 2 is the
+    // same promise for a ROW BLOCK of such a problem (x = rows of y, dK = those rows of a symmetric
+    // matrix): row pass only, the caller doubles and sums over row blocks.
+    if (symmetric == 0 && (dy || dscale)) {
         rc = run(y, x, 1, n2, n, dy, dscale, nullptr);
         if (rc) return rc;
     }
