@@ -34,7 +34,49 @@ def timed(fn, reps):
     t = torch.tensor([sorted(ts)[len(ts) // 2]], device="cuda", dtype=torch.float64)
     if dist.is_initialized():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    timed.last = ts
     return float(t.item())
+
+
+def breakdown(x, y, sc, var, ls, rank, world, block, r0, r1):
+    """Phases of one fit, each between device synchronisations (so overlap across phases is lost)."""
+    import time
+    n = x.shape[0]
+    out = {}
+
+    def lap(name, fn):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        r = fn()
+        torch.cuda.synchronize()
+        out[name] = (time.perf_counter() - t0) * 1e3
+        return r
+
+    for _ in range(2):
+        sw = sharded_gp.ShardedSweep(n, block, rank, world, None, x.device, True, sharded_gp.CudaKernels())
+        lap("assemble (Gram blocks)", lambda: sw.assemble("rbf", x, y, sc, var, ls))
+        lap("sweep (factor / broadcast / update)", sw.run)
+        lap("nll terms", sw.nll_terms)
+        alpha = lap("alpha", sw.alpha)
+        s = lap("gradient partial products", lambda: sw.grad_partial(False))
+        if world > 1:
+            def red():
+                a0 = 0
+                for r in range(world):
+                    b0 = n * (r + 1) // world
+                    dist.reduce(s[a0:b0], dst=r)
+                    a0 = b0
+            lap("row-block reduce", red)
+        dk = s[r0:r1]
+
+        def gb():
+            dk[:, :n].addr_(alpha[r0:r1], alpha, alpha=-0.5)
+            return sw.k.gram_bwd_rows("rbf", x[r0:r1].contiguous(), x, sc, var, dk, True, True)
+        lap("Gram backward (row block)", gb)
+        del sw, s, dk
+    return out
 
 
 def main():
@@ -43,6 +85,7 @@ def main():
     ap.add_argument("--d", type=int, default=128)
     ap.add_argument("--block", type=int, default=512)
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--breakdown", action="store_true", help="also time the phases separately (synchronising between them)")
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -72,8 +115,11 @@ def main():
 
         ms = timed(fit, a.reps)
         line = {"what": "exact-GP fit, sharded Gram + Cholesky sweep + gradients", "n": n, "d": a.d, "n_gpus": world,
-                "block": a.block, "fit_ms": ms, "loss": float(box["loss"]),
+                "block": a.block, "fit_ms": ms, "fit_ms_rank0_reps": timed.last, "loss": float(box["loss"]),
                 "info": int(sharded_gp._ShardedExactGPLoss.last_info.item())}
+        if a.breakdown:
+            line["phases_ms"] = breakdown(x.to(dev), y.to(dev).reshape(-1), sc.detach(), var.detach().reshape(1),
+                                          ls.detach().reshape(1), rank, world, a.block, r0, r1)
         if world == 1:
             xf = x.to(dev).requires_grad_(True)
             yf = y.to(dev)

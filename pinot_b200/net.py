@@ -92,8 +92,10 @@ class Net(BaseNet):
         from . import ops
         reg = self.output_regressor
         with torch.no_grad():
-            h_last = self.representation(self.g_last)
-            post = ops.ExactGPPosterior(h_last, self.y_last, reg.kernel.scale, reg.kernel.variance, reg.log_sigma,
+            h_last, y_last = self.representation(self.g_last), self.y_last
+            if hasattr(reg, "_gathered"):      # sharded head: condition on every rank's training rows
+                h_last, y_last = reg._gathered(h_last, y_last)
+            post = ops.ExactGPPosterior(h_last, y_last, reg.kernel.scale, reg.kernel.variance, reg.log_sigma,
                                         kind=reg._kind(), check=bool(reg.check_positive_definite))
             nb = g.batch_size
             means, variances = [], []

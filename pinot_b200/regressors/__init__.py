@@ -5,5 +5,6 @@ from .neural_network_regressor import NeuralNetworkRegressor  # noqa: F401
 from .gaussian_process_regressor import (  # noqa: F401
     GaussianProcessRegressor,
     ExactGaussianProcessRegressor,
+    ShardedExactGaussianProcessRegressor,
     VariationalGaussianProcessRegressor,
 )

@@ -127,6 +127,53 @@ class ExactGaussianProcessRegressor(GaussianProcessRegressor):
         return torch.distributions.normal.Normal(loc=mean, scale=var.clamp_min(0).sqrt(), validate_args=False)
 
 
+class ShardedExactGaussianProcessRegressor(ExactGaussianProcessRegressor):
+    """Exact GP head over the UNION of all ranks' training rows (not in the reference, which is
+    single-device; arithmetic of gaussian_process_regressor.py:85-233 on the gathered rows).
+
+    ``loss(x_tr_local, y_tr_local)`` takes THIS rank's rows (the embeddings of its molecules), runs the
+    Gram matrix and the Cholesky sweep sharded by column blocks over the process group
+    (pinot_b200.sharded_gp) and returns the same (1, 1) value on every rank.  ``backward`` gives each rank
+    the gradient of its own rows; the kernel hyper-parameters and ``log_sigma`` receive per-rank partial
+    sums, so the data-parallel gradient all-reduce (``GradientBucket.allreduce(average=False)``) completes
+    them -- do not average.  ``condition`` / ``condition_marginal`` gather the training rows and predict
+    this rank's test rows with the replicated single-GPU posterior.
+    """
+
+    def __init__(self, in_features, kernel=None, log_sigma=-3.0, logdet="trace", group=None, block=512):
+        super(ShardedExactGaussianProcessRegressor, self).__init__(in_features, kernel=kernel, log_sigma=log_sigma,
+                                                                   logdet=logdet)
+        self.group = group
+        self.block = block
+
+    def loss(self, x_tr, y_tr, *args, **kwargs):
+        from .. import sharded_gp
+        self._x_tr = x_tr
+        self._y_tr = y_tr
+        loss = sharded_gp.sharded_exact_gp_loss(
+            x_tr, y_tr, self.kernel.scale, self.kernel.variance, self.log_sigma, kind=self._kind(),
+            exact_logdet=(self.logdet == "exact"), group=self.group, block=self.block,
+            check=(self.check_positive_definite is True))
+        self._last_info = sharded_gp._ShardedExactGPLoss.last_info
+        return loss
+
+    def _gathered(self, x_tr, y_tr):
+        from .. import sharded_gp
+        import torch.distributed as dist
+        world = dist.get_world_size(self.group) if (dist.is_available() and dist.is_initialized()) else 1
+        x_all, _ = sharded_gp._gather_rows(x_tr.detach().contiguous(), self.group, world)
+        y_all, _ = sharded_gp._gather_rows(y_tr.detach().reshape(x_tr.shape[0], -1).contiguous(), self.group, world)
+        return x_all, y_all
+
+    def condition(self, x_te, *args, x_tr=None, y_tr=None, **kwargs):
+        x_all, y_all = self._gathered(x_tr, y_tr)
+        return super(ShardedExactGaussianProcessRegressor, self).condition(x_te, x_tr=x_all, y_tr=y_all)
+
+    def condition_marginal(self, x_te, x_tr=None, y_tr=None):
+        x_all, y_all = self._gathered(x_tr, y_tr)
+        return super(ShardedExactGaussianProcessRegressor, self).condition_marginal(x_te, x_tr=x_all, y_tr=y_all)
+
+
 class VariationalGaussianProcessRegressor(GaussianProcessRegressor):
     """Sparse variational GP head (gaussian_process_regressor.py:236-508)."""
 

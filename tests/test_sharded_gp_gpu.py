@@ -55,6 +55,35 @@ def test_non_positive_definite_matrix_reports_the_global_pivot():
     assert int(sharded_gp._ShardedExactGPLoss.last_info.item()) > 0
 
 
+def test_sharded_head_inside_net_matches_exact_head():
+    import copy
+    import pinot_b200 as pb
+    from pinot_b200 import synthetic
+    from pinot_b200.regressors import ExactGaussianProcessRegressor, ShardedExactGaussianProcessRegressor
+    torch.manual_seed(0)
+    g, y = synthetic.make_batch(300, seed=5)
+    g, y = g.to(DEV), y.to(DEV)
+    gt, _ = synthetic.make_batch(40, seed=6)
+    gt = gt.to(DEV)
+    rep = pb.representation.Sequential(pb.representation.dgl_legacy.gn(), [64, "tanh", 64, "tanh"])
+    a = pb.Net(rep, output_regressor_class=ExactGaussianProcessRegressor).to(DEV)
+    b = pb.Net(copy.deepcopy(rep), output_regressor_class=ShardedExactGaussianProcessRegressor, block=128).to(DEV)
+    b.load_state_dict(a.state_dict())
+    for net in (a, b):
+        with torch.no_grad():
+            net.output_regressor.kernel.scale.fill_(-3.0)
+    la, lb = a.loss(g, y), b.loss(g, y)
+    la.sum().backward()
+    lb.sum().backward()
+    assert rel_err(lb, la) < 1e-5
+    for (name, pa), (_, pb_) in zip(a.named_parameters(), b.named_parameters()):
+        assert rel_err(pb_.grad, pa.grad) < 1e-3, name
+    da, db = a.condition(gt), b.condition(gt)
+    assert rel_err(db.mean, da.mean) < 1e-5
+    ma, mb = a.condition_marginal(gt), b.condition_marginal(gt)
+    assert rel_err(mb.mean, ma.mean) < 1e-5 and rel_err(mb.scale, ma.scale) < 1e-5
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
