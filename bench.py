@@ -43,6 +43,17 @@ def parse():
     return ap.parse_args()
 
 
+def ncu_traffic(kernel_key):
+    """DRAM bytes (read + write) per launch of a kernel from the committed ncu --set full capture
+    (profiles/r01/ncu_traffic.json, taken at the default workload), or None."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01", "ncu_traffic.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["kernels"][kernel_key]["dram_bytes_per_launch"])
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def workload_config(n_mol, world):
     return {
         "workload": "C2: %d synthetic molecules per GPU (25 atoms / 54 directed edges), GraphConv 3x128 + "
@@ -294,7 +305,7 @@ def b200_main(args):
                   "is the whole C-ABI call (hi/lo split pass + GEMM)" % n,
         "bound": "tensor", "achieved": grad_flop / (grad_ms * 1e-3) / 1e12 if grad_ms else None,
         "peak": tf_peak, "unit": "TFLOP/s", "peak_source": peak_src + ", bf16 sustained",
-        "traffic": None,
+        "traffic": ncu_traffic("tgemm_tma_kernel") if n == 4200 else None,
         "note": "algorithmic flops N^3/3 (triangular x triangular, symmetric output); the fp32-parity path "
                 "issues 3 TF32 MMAs per product, so the tensor pipe executes 3x these flops at the TF32 rate "
                 "(half the bf16 peak used as denominator): frac = 1/6 would be a saturated TF32 pipe",
