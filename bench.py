@@ -281,7 +281,8 @@ def b200_main(args):
     total_ms = pbd.max_over_ranks(sum(step_ms), dev)
     ms_per_step = total_ms / args.steps
     value = n_mol * world / (ms_per_step * 1e-3)
-    final_loss = float(loss)
+    final_loss = float(loss.detach())
+    del loss   # no live autograd graph: the CUDA-graph capture below needs fresh AccumulateGrad nodes
 
     # ---- per-kernel timings from the probes (CUDA events on the launching stream, timed region) ----
     def probe_ms(name):
@@ -345,6 +346,23 @@ def b200_main(args):
                 ev.record(copy_stream)
             return gs, yy, ev
 
+        # The step itself is replayed from a CUDA graph (pinot_b200.CapturedTrainStep, the public API for
+        # full-batch training): one launch call per step instead of ~150, so the host's only per-step work
+        # is the upload of the next batch.  Falls back to the eager step if the capture is refused.
+        captured, mode = None, "eager step"
+        try:
+            opt_c = torch.optim.Adam(net.parameters(), 1e-3, capturable=True)
+            g_static = g_host.to(dev)
+            g_static.csr()
+            captured = pb.CapturedTrainStep(net, opt_c, g_static, y_host.to(dev),
+                                            after_backward=lambda: bucket.allreduce(average=False))
+            mode = "CUDA-graph replay of the step (pinot_b200.CapturedTrainStep)"
+        except Exception as exc:  # noqa: BLE001 - any capture failure means: measure the eager path
+            sys.stderr.write("bench.py: CUDA-graph capture of the step failed (%s); e2e uses the eager step\n" % exc)
+            captured = None
+
+        step_marks = []
+
         def e2e_loop(n_steps):
             """Every step uploads its own inputs from pinned host memory and reads its loss back;
             the upload of step k+1 overlaps the compute of step k (two-deep pipeline)."""
@@ -352,22 +370,51 @@ def b200_main(args):
             for k in range(n_steps):
                 gs, yy, ev = nxt
                 torch.cuda.current_stream().wait_event(ev)
-                loss_dev = step(gs, yy)                  # asynchronous launches
+                ta = time.perf_counter()
+                if captured is not None:
+                    captured.load(gs, yy)                # device copy into the captured inputs
+                    loss_dev = captured()                # one graph launch
+                else:
+                    loss_dev = step(gs, yy)              # asynchronous launches
+                tb = time.perf_counter()
                 if k + 1 < n_steps:
                     nxt = upload()                       # next step's H2D + index build meanwhile
+                tc = time.perf_counter()
                 loss_host = float(loss_dev.item())       # device -> host read of the loss
                 net.output_regressor.verify()
+                step_marks.append(time.perf_counter())
+                if os.environ.get("PINOT_B200_BENCH_DEBUG"):
+                    sys.stderr.write("e2e step %d: launch %.2f ms, upload %.2f ms, wait %.2f ms\n" % (
+                        k, 1e3 * (tb - ta), 1e3 * (tc - tb), 1e3 * (step_marks[-1] - tc)))
             return loss_host
 
-        e2e_loop(2)
+        import gc
+        e2e_loop(5)
+        gc.collect()
+        gc.disable()                                     # no collector pauses inside the timed loop
         barrier()
         t0 = time.perf_counter()
         e2e_loop(args.steps)
         barrier()
         e2e_s = pbd.max_over_ranks(time.perf_counter() - t0, dev)
+        gc.enable()
         e2e = {"value": n_mol * world * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
-               "d2h_bytes_per_step": 4, "ms_per_step": 1e3 * e2e_s / args.steps,
+               "d2h_bytes_per_step": 4, "ms_per_step": 1e3 * e2e_s / args.steps, "mode": mode,
                "includes": "per step: H2D of edges/features/targets from pinned memory + CSR build (copy stream, overlapping the previous step), train step, loss.item()"}
+        marks = step_marks[-args.steps:]
+        e2e["per_step_ms"] = [round(1e3 * (b - a), 3) for a, b in zip([t0] + marks[:-1], marks)]
+        if captured is not None:
+            # the same replay with resident inputs, device-timed like `value` (L2 flushed between steps)
+            ts = []
+            for _ in range(args.steps):
+                flush_buf.zero_()
+                s_ev, e_ev = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                s_ev.record()
+                captured()
+                e_ev.record()
+                torch.cuda.synchronize()
+                ts.append(s_ev.elapsed_time(e_ev))
+            e2e["captured_step_device_ms"] = pbd.max_over_ranks(sum(ts) / len(ts), dev)
 
     # ---- second headline number of BASELINE.json: exact-GP fit at N = 16 384 (embeddings given):
     #      Gram + sweep (factor, L^-1 y, L^-T) + NLL + closed-form gradients, one GPU ----

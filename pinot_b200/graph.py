@@ -57,6 +57,22 @@ class GraphCSR:
             self._has_zero_in_degree = bool((self._in_deg == 0).any().item()) if self.num_nodes else False
         return self._has_zero_in_degree
 
+    _TENSORS = ("indices", "indptr", "indices_t", "indptr_t", "in_norm", "out_norm", "inv_in_deg", "seg_offsets",
+                "node_seg", "_in_deg")
+
+    def copy_from_(self, other):
+        """Overwrite this view's device arrays with another graph's (same node / edge / graph counts):
+        the addresses stay, which is what a captured CUDA graph of the train step needs."""
+        if (self.num_nodes, self.batch_size, self.indices.numel()) != (other.num_nodes, other.batch_size,
+                                                                       other.indices.numel()):
+            raise ValueError("copy_from_: graphs differ in size (%d nodes / %d edges / %d graphs vs %d / %d / %d)" % (
+                self.num_nodes, self.indices.numel(), self.batch_size, other.num_nodes, other.indices.numel(),
+                other.batch_size))
+        for name in self._TENSORS:
+            getattr(self, name).copy_(getattr(other, name), non_blocking=True)
+        self._has_zero_in_degree = other._has_zero_in_degree
+        return self
+
     def scales(self, norm):
         if norm == "both":
             return self.out_norm, self.in_norm
@@ -198,6 +214,25 @@ class BatchedGraph:
         g._csr = self._csr if (self._csr is not None and torch.device(device) == self._src.device) else None
         g._off = None
         return g
+
+    def copy_from_(self, other):
+        """In-place copy of another batched graph with the same node / edge / graph counts (structure,
+        kernel views and node / edge data); every device address of this graph stays valid."""
+        if self._src.numel() != other._src.numel() or self._num_nodes != other._num_nodes or \
+                len(self._bnn) != len(other._bnn):
+            raise ValueError("copy_from_: graphs differ in size")
+        self._src.copy_(other._src, non_blocking=True)
+        self._dst.copy_(other._dst, non_blocking=True)
+        self._bnn, self._bne = list(other._bnn), list(other._bne)
+        self._off = None
+        self.csr().copy_from_(other.csr())
+        for frame, oframe in ((self.ndata, other.ndata), (self.edata, other.edata)):
+            for k, v in oframe.items():
+                if torch.is_tensor(v) and k in frame and frame[k].shape == v.shape:
+                    frame[k].copy_(v, non_blocking=True)
+                else:
+                    dict.__setitem__(frame, k, v.to(self._src.device) if torch.is_tensor(v) else v)
+        return self
 
     @contextlib.contextmanager
     def local_scope(self):

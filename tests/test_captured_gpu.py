@@ -1,0 +1,62 @@
+"""CapturedTrainStep: the CUDA-graph replay of the train step must follow the eager step exactly."""
+import copy
+
+import pytest
+import torch
+
+import pinot_b200 as pb
+from pinot_b200 import synthetic
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _net(seed=0):
+    torch.manual_seed(seed)
+    rep = pb.representation.Sequential(pb.representation.dgl_legacy.gn(), [64, "tanh", 64, "tanh"])
+    net = pb.Net(rep, output_regressor_class=pb.regressors.ExactGaussianProcessRegressor).to(DEV)
+    with torch.no_grad():
+        net.output_regressor.kernel.scale.fill_(-3.0)
+    return net
+
+
+def test_replay_follows_eager_training_and_load_swaps_the_batch():
+    g, y = synthetic.make_batch(256, seed=11)
+    g, y = g.to(DEV), y.to(DEV)
+    eager = _net()
+    captured = copy.deepcopy(eager)
+    opt_e = torch.optim.Adam(eager.parameters(), 1e-3)
+    opt_c = torch.optim.Adam(captured.parameters(), 1e-3, capturable=True)
+    before = [p.detach().clone() for p in captured.parameters()]
+    step = pb.CapturedTrainStep(captured, opt_c, g, y)
+    for p, b in zip(captured.parameters(), before):
+        assert torch.equal(p, b), "construction must not train"
+    # a second batch with the same structure but different features / targets
+    g2 = g.to(DEV)
+    g2.ndata["h"] = g.ndata["h"] * 0.5 + 0.1
+    g2.csr()
+    y2 = -y
+    for it in range(4):
+        if it == 2:
+            step.load(g2, y2)
+        ge, ye = (g, y) if it < 2 else (g2, y2)
+        opt_e.zero_grad(set_to_none=True)
+        le = eager.loss(ge, ye).sum()
+        le.backward()
+        opt_e.step()
+        lc = step()
+        captured.output_regressor.verify()
+        assert rel_err(lc, le) < 1e-5, it
+    for (name, pe), (_, pc) in zip(eager.named_parameters(), captured.named_parameters()):
+        assert rel_err(pc, pe) < 1e-4, name
+
+
+def test_load_rejects_a_batch_of_another_size():
+    g, y = synthetic.make_batch(64, seed=1)
+    g, y = g.to(DEV), y.to(DEV)
+    net = _net()
+    step = pb.CapturedTrainStep(net, torch.optim.Adam(net.parameters(), 1e-3, capturable=True), g, y)
+    other, yo = synthetic.make_batch(65, seed=2)
+    with pytest.raises(ValueError, match="differ in size"):
+        step.load(other.to(DEV), yo.to(DEV))
