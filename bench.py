@@ -415,6 +415,8 @@ def b200_main(args):
                 torch.cuda.synchronize()
                 ts.append(s_ev.elapsed_time(e_ev))
             e2e["captured_step_device_ms"] = pbd.max_over_ranks(sum(ts) / len(ts), dev)
+            captured.release()     # the graph holds the NCCL all-reduce: it must go before the process group
+            captured = None
 
     # ---- second headline number of BASELINE.json: exact-GP fit at N = 16 384 (embeddings given):
     #      Gram + sweep (factor, L^-1 y, L^-T) + NLL + closed-form gradients, one GPU ----

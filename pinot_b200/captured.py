@@ -86,3 +86,13 @@ class CapturedTrainStep:
     def __call__(self):
         self.graph.replay()
         return self.loss
+
+    def release(self):
+        """Destroy the captured graph and its memory pool.  Required before
+        ``torch.distributed.destroy_process_group()`` when the step contains an NCCL collective: the
+        communicator cannot be torn down while a graph that references it is alive."""
+        torch.cuda.synchronize()
+        if self.graph is not None:
+            self.graph.reset()
+        self.graph = None
+        self.loss = None
