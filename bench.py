@@ -330,21 +330,38 @@ def b200_main(args):
         feat_h = g_host.ndata["h"].pin_memory()
         y_h = y_host.pin_memory()
         bnn, bne = g_host.batch_num_nodes().tolist(), g_host.batch_num_edges().tolist()
-        h2d = sum(t.numel() * t.element_size() for t in (src_h, dst_h, feat_h, y_h))
+        h2d = sum(t.numel() * t.element_size() for t in (src_h, dst_h, feat_h, y_h)) + 8 * len(bnn)
 
-        copy_stream = torch.cuda.Stream(device=dev)
+        copy_stream = torch.cuda.Stream(device=dev, priority=-1)   # its small kernels go ahead of the step's
+        # two staging slots on the device, reused every other step (no per-step large allocations)
+        bnn_h = g_host.batch_num_nodes().to(torch.long).pin_memory()
+        stage = [tuple(torch.empty_like(t, device=dev) for t in (src_h, dst_h, feat_h, y_h, bnn_h)) for _ in range(2)]
+        n_up = [0]
 
         def upload():
             """H2D of one step's inputs + graph index build, on the copy stream."""
+            s_d, d_d, f_d, y_d, b_d = stage[n_up[0] % 2]
+            n_up[0] += 1
+            t_ = [time.perf_counter()]
             with torch.cuda.stream(copy_stream):
-                gs = BatchedGraph(src_h.to(dev, non_blocking=True), dst_h.to(dev, non_blocking=True),
-                                  g_host.number_of_nodes(), bnn, bne, validate=False)
-                gs.ndata["h"] = feat_h.to(dev, non_blocking=True)
-                yy = y_h.to(dev, non_blocking=True)
+                s_d.copy_(src_h, non_blocking=True)
+                d_d.copy_(dst_h, non_blocking=True)
+                f_d.copy_(feat_h, non_blocking=True)
+                y_d.copy_(y_h, non_blocking=True)
+                b_d.copy_(bnn_h, non_blocking=True)
+                t_.append(time.perf_counter())
+                gs = BatchedGraph(s_d, d_d, g_host.number_of_nodes(), bnn, bne, validate=False,
+                                  batch_num_nodes_device=b_d)
+                gs.ndata["h"] = f_d
+                t_.append(time.perf_counter())
                 gs.csr()
+                t_.append(time.perf_counter())
                 ev = torch.cuda.Event()
                 ev.record(copy_stream)
-            return gs, yy, ev
+            if os.environ.get("PINOT_B200_BENCH_DEBUG") and t_[-1] - t_[0] > 6e-3:
+                sys.stderr.write("slow upload: copies %.2f ms, graph %.2f ms, csr %.2f ms\n" % tuple(
+                    1e3 * (b - a) for a, b in zip(t_[:-1], t_[1:])))
+            return gs, y_d, ev
 
         # The step itself is replayed from a CUDA graph (pinot_b200.CapturedTrainStep, the public API for
         # full-batch training): one launch call per step instead of ~150, so the host's only per-step work

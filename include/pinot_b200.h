@@ -61,6 +61,21 @@ PINOT_B200_API int pinot_b200_mp_csr_aggregate_bwd(const float* dout, float* dx,
                                     const float* dst_scale, int64_t n_src, int64_t feat,
                                     cudaStream_t stream);
 
+/* Graph index build from a batched edge list (device int64 src / dst in DGL's batched numbering,
+ * pinot/graph.py:238-239 + dgl.batch via pinot/data/utils.py:260-276): CSR by destination
+ * (indptr / indices) and by source (indptr_t / indices_t) with the original edge order kept inside
+ * every row (= a stable sort by the row key), in_norm / out_norm = clamp(deg, 1)^-1/2 (GraphConv
+ * norm="both"), inv_in_deg = 1 / clamp(in_deg, 1) (SAGEConv "mean"), in_deg (int64), seg_offsets =
+ * exclusive scan of batch_num_nodes (n_graphs + 1) and node_seg = graph of every node (dgl.sum_nodes).
+ * Replaces the torch sort / bincount / cumsum sequence a DGL graph object performs lazily; one call,
+ * no host synchronisation.  Edges with an endpoint outside [0, n_nodes) are skipped.
+ * Limits: n_nodes, n_graphs <= 67 108 864.  workspace >= pinot_b200_csr_build_workspace_bytes(...). */
+PINOT_B200_API int64_t pinot_b200_csr_build_workspace_bytes(int64_t n_nodes, int64_t n_edges);
+PINOT_B200_API int pinot_b200_csr_build(const int64_t* src, const int64_t* dst, int64_t n_edges, int64_t n_nodes,
+                         const int64_t* batch_num_nodes, int64_t n_graphs, int32_t* indptr, int32_t* indices,
+                         int32_t* indptr_t, int32_t* indices_t, float* in_norm, float* out_norm,
+                         float* inv_in_deg, int64_t* in_deg, int32_t* seg_offsets, int32_t* node_seg,
+                         void* workspace, int64_t workspace_bytes, cudaStream_t stream);
 /* Row gather out[i,:] = x[idx[i],:] (idx: int64, device).  The data movement of re-batching a
  * selection of molecules, i.e. of dgl.batch([dgl.unbatch(g)[i] for i in idxs]) in
  * pinot/active/experiment.py:83-104 (_slice_fn_graph). */

@@ -24,6 +24,8 @@ SIGNATURES = {
     "pinot_b200_launch_count": [],
     "pinot_b200_mp_csr_aggregate_fwd": [_ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i64, _ptr],
     "pinot_b200_mp_csr_aggregate_bwd": [_ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i64, _ptr],
+    "pinot_b200_csr_build_workspace_bytes": [_i64, _i64],
+    "pinot_b200_csr_build": [_ptr, _ptr, _i64, _i64, _ptr, _i64] + [_ptr] * 10 + [_ptr, _i64, _ptr],
     "pinot_b200_gather_rows": [_ptr, _ptr, _ptr, _i64, _i64, _ptr],
     "pinot_b200_segment_readout_fwd": [_ptr, _ptr, _ptr, _i64, _i64, _i32, _ptr],
     "pinot_b200_segment_readout_bwd": [_ptr, _ptr, _ptr, _ptr, _i64, _i64, _i32, _ptr],
@@ -53,6 +55,7 @@ _RESTYPES = {
     "pinot_b200_potrf_workspace_bytes": ctypes.c_int64,
     "pinot_b200_sgemm_nt_tma_workspace_bytes": ctypes.c_int64,
     "pinot_b200_potrf_tma_scratch_bytes": ctypes.c_int64,
+    "pinot_b200_csr_build_workspace_bytes": ctypes.c_int64,
     "pinot_b200_gp_nll_grad_workspace_bytes": ctypes.c_int64,
     "pinot_b200_launch_count": ctypes.c_int64,
 }

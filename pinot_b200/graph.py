@@ -9,7 +9,12 @@ views consumed by the kernels are derived once per graph and cached.
 """
 import contextlib
 
+import os
+
 import torch
+
+
+_KERNEL_BUILD_MAX_NODES = 4096 * 16384   # limit of pinot_b200_csr_build's two-level scan
 
 
 class GraphCSR:
@@ -22,8 +27,46 @@ class GraphCSR:
             raise ValueError("pinot_b200: graphs are limited to 2^31 nodes / edges (int32 CSR)")
         src = src.long()
         dst = dst.long()
-        in_deg = torch.bincount(dst, minlength=n)
-        out_deg = torch.bincount(src, minlength=n)
+        self.num_nodes = n
+        self._has_zero_in_degree = None
+        if dev.type == "cuda" and os.environ.get("PINOT_B200_CSR", "kernel") != "torch" and n <= _KERNEL_BUILD_MAX_NODES:
+            self._build_with_kernel(src.contiguous(), dst.contiguous(), n, batch_num_nodes)
+        else:
+            self._build_with_torch(src, dst, n, batch_num_nodes)
+
+    def _build_with_kernel(self, src, dst, n, batch_num_nodes):
+        """One C-ABI call (pinot_b200_csr_build): counting sort with DGL's edge order kept inside rows,
+        degree vectors, graph offsets; asynchronous on the current stream, no host synchronisation."""
+        from . import _lib
+        dev = src.device
+        bnn = torch.as_tensor(batch_num_nodes, dtype=torch.long)
+        self.batch_size = int(bnn.numel())
+        if not bnn.is_cuda:
+            bnn = bnn.pin_memory().to(dev, non_blocking=True)   # a pageable copy would block the host
+        ne = int(src.numel())
+        i32 = dict(dtype=torch.int32, device=dev)
+        f32 = dict(dtype=torch.float32, device=dev)
+        self.indptr, self.indices = torch.empty(n + 1, **i32), torch.empty(ne, **i32)
+        self.indptr_t, self.indices_t = torch.empty(n + 1, **i32), torch.empty(ne, **i32)
+        self.in_norm, self.out_norm, self.inv_in_deg = (torch.empty(n, **f32) for _ in range(3))
+        self._in_deg = torch.empty(n, dtype=torch.long, device=dev)
+        self.seg_offsets = torch.empty(self.batch_size + 1, **i32)
+        self.node_seg = torch.empty(n, **i32)
+        ws_bytes = int(_lib.load().pinot_b200_csr_build_workspace_bytes(n, ne))
+        ws = torch.empty(ws_bytes // 4, **i32)
+        _lib.call("csr_build", _lib.ptr(src), _lib.ptr(dst), ne, n, _lib.ptr(bnn), self.batch_size,
+                  _lib.ptr(self.indptr), _lib.ptr(self.indices), _lib.ptr(self.indptr_t), _lib.ptr(self.indices_t),
+                  _lib.ptr(self.in_norm), _lib.ptr(self.out_norm), _lib.ptr(self.inv_in_deg), _lib.ptr(self._in_deg),
+                  _lib.ptr(self.seg_offsets), _lib.ptr(self.node_seg), _lib.ptr(ws), ws_bytes)
+
+    def _build_with_torch(self, src, dst, n, batch_num_nodes):
+        """The same index in torch ops (CPU graphs, and the cross-check of the kernel path)."""
+        dev = src.device
+        # degree counts by scatter-add: torch.bincount reads its maximum back to the host, which would
+        # stall an asynchronous upload pipeline on every graph
+        ones = torch.ones_like(dst)
+        in_deg = torch.zeros(n, dtype=torch.long, device=dev).scatter_add_(0, dst, ones)
+        out_deg = torch.zeros(n, dtype=torch.long, device=dev).scatter_add_(0, src, ones)
         # CSR by destination (forward gather) and by source (transposed graph, backward gather);
         # stable sorts keep DGL's edge order inside every row.
         order = torch.sort(dst, stable=True).indices
@@ -39,16 +82,19 @@ class GraphCSR:
         self.out_norm = out_deg.float().clamp(min=1).pow(-0.5).contiguous()
         # SAGEConv("mean"): mean over in-neighbours, 0 for isolated nodes
         self.inv_in_deg = (1.0 / in_deg.float().clamp(min=1)).contiguous()
-        bnn = torch.as_tensor(batch_num_nodes, dtype=torch.long, device=dev)
+        bnn = torch.as_tensor(batch_num_nodes, dtype=torch.long)
+        if dev.type == "cuda" and not bnn.is_cuda:
+            # pinned + non_blocking: a pageable copy would block the host until the stream drains
+            bnn = bnn.pin_memory().to(dev, non_blocking=True)
+        else:
+            bnn = bnn.to(dev)
         self.batch_size = int(bnn.numel())
         self.seg_offsets = torch.zeros(self.batch_size + 1, dtype=torch.int32, device=dev)
         self.seg_offsets[1:] = torch.cumsum(bnn, 0).to(torch.int32)
         self.node_seg = torch.repeat_interleave(
             torch.arange(self.batch_size, device=dev, dtype=torch.int32), bnn, output_size=n
         ).contiguous()
-        self.num_nodes = n
         self._in_deg = in_deg
-        self._has_zero_in_degree = None
 
     @property
     def has_zero_in_degree(self):
@@ -103,7 +149,11 @@ class BatchedGraph:
     code (pinot/representation/sequential.py:78-103, pinot/data/utils.py:260-276,
     pinot/active/experiment.py:99-104)."""
 
-    def __init__(self, src=None, dst=None, num_nodes=0, batch_num_nodes=None, batch_num_edges=None, validate=True):
+    def __init__(self, src=None, dst=None, num_nodes=0, batch_num_nodes=None, batch_num_edges=None, validate=True,
+                 batch_num_nodes_device=None):
+        #: optional int64 device copy of batch_num_nodes (an upload pipeline copies it alongside the edges,
+        #: so that building the kernel views needs no host->device transfer of its own)
+        self._bnn_dev = batch_num_nodes_device
         self._src = torch.zeros(0, dtype=torch.long) if src is None else torch.as_tensor(src, dtype=torch.long)
         self._dst = torch.zeros(0, dtype=torch.long) if dst is None else torch.as_tensor(dst, dtype=torch.long).to(self._src.device)
         if self._src.shape != self._dst.shape:
@@ -307,7 +357,9 @@ class BatchedGraph:
     # -- kernel view ----------------------------------------------------------------------------
     def csr(self):
         if self._csr is None:
-            self._csr = GraphCSR(self._src, self._dst, self._num_nodes, self._bnn)
+            bnn_dev = getattr(self, "_bnn_dev", None)
+            use_dev = bnn_dev is not None and bnn_dev.device == self._src.device and bnn_dev.numel() == len(self._bnn)
+            self._csr = GraphCSR(self._src, self._dst, self._num_nodes, bnn_dev if use_dev else self._bnn)
         return self._csr
 
 
