@@ -48,4 +48,10 @@ bool gemm_uses_tensor_cores();
 // Launches the GEMM on `stream`.  Returns PB_OK or an error code (message via set_error).
 int gemm(const GemmParams& p, cudaStream_t stream);
 
+// gemm_node.cu: persistent TMA-fed kernel for M >> N, K with N, K <= 128 (node-update layers); gemm() routes
+// to it when applicable (PINOT_B200_NODE_GEMM=0 switches it off).
+bool node_gemm_applicable(const GemmParams& g);
+int launch_node_gemm(const GemmParams& g, cudaStream_t stream);
+bool gemm_tma_enabled();
+
 }  // namespace pb

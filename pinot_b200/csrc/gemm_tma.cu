@@ -15,6 +15,7 @@
 // (TMEM accumulation truncates, see gemm_tc.cu), so flushing chunk c overlaps the MMAs of chunk c+1.
 #include "gemm_params.cuh"
 #include "gemm_epilogue.cuh"
+#include "tma_common.cuh"
 #include <cuda.h>
 #include "../../include/pinot_b200.h"
 #include <stdlib.h>
@@ -22,6 +23,8 @@
 namespace pb {
 
 namespace {
+
+using namespace tc;
 
 constexpr int BM = 128, BN = 128, BK = 32, NSTAGE = 3;
 constexpr int TILE_BYTES = BM * BK * 4;            // 16 KB: 128 rows x 128 bytes, SWIZZLE_128B
@@ -32,58 +35,6 @@ constexpr int NTHREADS = 192;                      // producer, MMA, 4 epilogue 
 constexpr int KCHUNK = 512;
 constexpr int STAGES_PER_CHUNK = KCHUNK / BK;
 constexpr int NSCHED = 4;                          // depth of the tile hand-off ring
-
-__device__ __forceinline__ uint32_t s32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "WAIT_LOOP:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra DONE;\n\t"
-        "bra WAIT_LOOP;\n\t"
-        "DONE:\n\t"
-        "}\n" ::"r"(s32(bar)), "r"(parity)
-        : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(s32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int x, int y, uint64_t* bar) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
-            s32(dst)),
-        "l"(map), "r"(x), "r"(y), "r"(s32(bar))
-        : "memory");
-}
-// K-major, SWIZZLE_128B shared-memory matrix descriptor (8 rows x 128 B atoms, SBO = 1024 B).
-__device__ __forceinline__ uint64_t sw128_desc(uint32_t saddr) {
-    uint64_t d = 0;
-    d |= (uint64_t)((saddr >> 4) & 0x3FFF);
-    d |= (uint64_t)1 << 16;                 // LBO: unused for swizzled K-major layouts
-    d |= (uint64_t)(1024 >> 4) << 32;       // SBO
-    d |= (uint64_t)1 << 46;                 // descriptor version (sm_100)
-    d |= (uint64_t)2 << 61;                 // SWIZZLE_128B
-    return d;
-}
-__device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
-        "}\n" ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-__device__ __forceinline__ void mma_commit(uint64_t* bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(s32(bar)) : "memory");
-}
 
 // Live tiles in dispatch order.  Without `lower` the gm x gn rectangle row by row; with it only tiles on or
 // below the diagonal (row i has min(i + 1, gn) of them), still row by row -- for a ktri product that is
@@ -361,47 +312,6 @@ split_tf32_kernel(const float* __restrict__ x, int64_t ldx, float* __restrict__ 
     *reinterpret_cast<float4*>(lo + r * ldo + c) = l;
 }
 
-int num_sms() {
-    static const int n = [] {
-        int dev = 0, v = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess) return 148;
-        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) return 148;
-        return v;
-    }();
-    return n;
-}
-
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-EncodeTiledFn encode_fn() {
-    static EncodeTiledFn fn = [] {
-        void* f = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
-            q != cudaDriverEntryPointSuccess)
-            f = nullptr;
-        return reinterpret_cast<EncodeTiledFn>(f);
-    }();
-    return fn;
-}
-
-// 2-D map over a row-major fp32 array (rows x cols, leading dimension ld): box = 32 columns x 128 rows.
-int make_map(CUtensorMap* map, const float* base, int64_t rows, int64_t cols, int64_t ld) {
-    EncodeTiledFn fn = encode_fn();
-    PB_REQUIRE(fn != nullptr, "gemm (TMA): cuTensorMapEncodeTiled is not available from this driver");
-    const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-    const cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
-    const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)BM};
-    const cuuint32_t estr[2] = {1, 1};
-    const CUresult rc = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
-                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    PB_REQUIRE(rc == CUDA_SUCCESS, "gemm (TMA): cuTensorMapEncodeTiled failed with code %d", (int)rc);
-    return PB_OK;
-}
-
 }  // namespace
 
 // hi / lo copies plus 64 floats (256 bytes) for the tile counter, which sits FIRST
@@ -440,10 +350,10 @@ int launch_gemm_tma_presplit(const KParams& p, const float* a_hi, const float* a
     PB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm (TMA): empty product");
     alignas(64) CUtensorMap mah, mal, mbh, mbl;
     int rc;
-    if ((rc = make_map(&mah, a_hi, M, K, ldk))) return rc;
-    if ((rc = make_map(&mal, a_lo, M, K, ldk))) return rc;
-    if ((rc = make_map(&mbh, b_hi, N, K, ldk))) return rc;
-    if ((rc = make_map(&mbl, b_lo, N, K, ldk))) return rc;
+    if ((rc = make_map_box(&mah, a_hi, M, K, ldk))) return rc;
+    if ((rc = make_map_box(&mal, a_lo, M, K, ldk))) return rc;
+    if ((rc = make_map_box(&mbh, b_hi, N, K, ldk))) return rc;
+    if ((rc = make_map_box(&mbl, b_lo, N, K, ldk))) return rc;
     TileGrid tg;
     tg.gm = (int)ceil_div(M, BM); tg.gn = (int)ceil_div(N, BN); tg.lower = p.lower;
     const int ntiles = tg.count();

@@ -120,6 +120,47 @@ def test_node_update_large_rows_uses_split_k_weight_gradient():
     assert rel_err(b.grad, dz.sum(0)) < 1e-5
 
 
+@pytest.mark.parametrize("n,fin,fout", [(20000, 128, 128), (9001, 128, 32), (8200, 64, 128), (12345, 36, 20)])
+@pytest.mark.parametrize("w_is_out_in", [True, False])
+@pytest.mark.parametrize("act", [None, "tanh"])
+def test_node_update_tall_inputs_take_the_persistent_tma_kernel(n, fin, fout, w_is_out_in, act):
+    """n >= 8192 rows with at most 128 features go through gemm_node.cu (forward and dX); same answers as
+    fp64, and the same as the register-staged kernel it replaces (PINOT_B200_NODE_GEMM=0 is read once per
+    process, so that comparison is on a row count below the switch-over)."""
+    torch.manual_seed(n + fin)
+    x = torch.randn(n, fin)
+    w = torch.randn(fout, fin) * 0.1 if w_is_out_in else torch.randn(fin, fout) * 0.1
+    b = torch.randn(fout)
+    go = torch.randn(n, fout)
+    xd, wd, bd = (t.to(DEV).requires_grad_(True) for t in (x, w, b))
+    got = ops.node_update(xd, wd, bd, w_is_out_in=w_is_out_in, act=act)
+    got.backward(go.to(DEV))
+    wm = (w.t() if w_is_out_in else w).double()
+    want = x.double() @ wm + b.double()
+    dz = go.double()
+    if act:
+        want = torch.tanh(want)
+        dz = dz * (1 - want * want)
+    assert rel_err(got, want) < 2e-6
+    assert rel_err(xd.grad, dz @ wm.t()) < 1e-5
+    assert rel_err(bd.grad, dz.sum(0)) < 1e-5
+    # rows below the switch-over run on the other kernel: the shared rows must agree to the last bits
+    small = ops.node_update(xd[:4000].detach(), wd.detach(), bd.detach(), w_is_out_in=w_is_out_in, act=act)
+    assert rel_err(got[:4000], small) < 1e-6
+
+
+def test_node_update_tall_accumulate_and_ragged_tail():
+    torch.manual_seed(3)
+    n = 8192 + 77                                   # last row tile is partial
+    x, hn = torch.randn(n, 128, device=DEV), torch.randn(n, 128, device=DEV)
+    ws, wn = torch.randn(64, 128, device=DEV) * 0.1, torch.randn(64, 128, device=DEV) * 0.1
+    bs, bn = torch.randn(64, device=DEV), torch.randn(64, device=DEV)
+    y = ops.node_update(x, ws, bs, w_is_out_in=True)
+    y = ops.node_update(hn, wn, bn, y_prev=y, w_is_out_in=True, act="tanh")
+    want = torch.tanh(x.double() @ ws.double().t() + bs.double() + hn.double() @ wn.double().t() + bn.double())
+    assert rel_err(y, want) < 2e-6
+
+
 def test_node_update_accumulate_for_sage():
     torch.manual_seed(1)
     x, hn = torch.randn(200, 64, device=DEV), torch.randn(200, 64, device=DEV)
