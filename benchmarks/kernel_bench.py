@@ -85,6 +85,17 @@ def main():
                     "frac_bf16_peak": 2.0 * m * n * k / ms / 1e9 / tf})
         del a, w
 
+    # (2b) node update proper: tanh(X W^T + b), one row per atom, HBM roofline = read X + write Y
+    for (m, k, n) in [(nn_, 128, 128)] + ([] if quick else [(1000000, 128, 128), (4000000, 128, 128)]):
+        xx = torch.randn(m, k, device=DEV)
+        ww = torch.randn(n, k, device=DEV) * 0.1
+        bb = torch.randn(n, device=DEV)
+        ms = timeit(lambda: ops.node_update(xx, ww, bb, w_is_out_in=True, act="tanh"), flush=flush)
+        byts = 4.0 * m * (k + n) + 4.0 * k * n
+        out.append({"kernel": "node_update_fwd (tanh)", "rows": m, "in": k, "out": n, "ms": ms, "GBps": byts / ms / 1e6,
+                    "frac_hbm": byts / ms / 1e6 / hbm})
+        del xx, ww, bb
+
     # (3) Gram forward / backward, (4) sweep and the full exact-GP fit
     for n in ([1128, 4200] if quick else [1128, 4200, 16384]):
         d = 128
