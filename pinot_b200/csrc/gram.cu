@@ -284,11 +284,8 @@ int launch_bwd(int kind, const float* x, const float* y, const float* scale, int
                const float* variance, const float* dK, int64_t ldk, int trans, int64_t N, int64_t Np,
                int D, float* dx, float* dscale, float* dvariance, int vec_in, cudaStream_t stream) {
     const size_t smem = sizeof(float) * (size_t)(2 * DT * LDS_ + TS * LDS_ + DT);
-    static bool configured = false;
-    if (!configured) {
-        PB_CUDA(cudaFuncSetAttribute(gram_bwd_kernel<DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
-    }
+    // set on every launch: the attribute is per device, and a process may drive several
+    PB_CUDA(cudaFuncSetAttribute(gram_bwd_kernel<DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t itiles = pb::ceil_div(N, TS), jtiles = pb::ceil_div(Np, TS);
     int64_t js = pb::ceil_div(592, itiles);  // aim for ~4 CTAs per SM worth of blocks
     if (js > jtiles) js = jtiles;
