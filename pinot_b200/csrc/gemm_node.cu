@@ -32,7 +32,6 @@ constexpr int B_BYTES = 2 * MAX_SLABS * SLAB_BYTES; // hi | lo, 128 KB
 constexpr int RAW_BYTES = NRAW * SLAB_BYTES;        // 48 KB
 constexpr int OP_BYTES = NOP * 2 * SLAB_BYTES;      // per buffer: hi | lo
 constexpr int SMEM_BYTES = B_BYTES + RAW_BYTES + OP_BYTES;   // 224 KB (+ 1 KB static) of the 227 KB a CTA may have
-constexpr int PF_AHEAD = 3;                         // L2 prefetch distance, in tiles of this CTA
 constexpr int NTHREADS = 448;                       // producer, MMA, 8 epilogue warps, 4 converter warps
 constexpr int EPI_WARPS = 8, CONV_WARP0 = 2 + EPI_WARPS;
 constexpr int BTASKS = (BM * MAX_SLABS * 8 + NTHREADS - 1) / NTHREADS;   // 16-byte chunks of B per thread
@@ -99,10 +98,15 @@ node_gemm_kernel(const KParams p, const int transB, const __grid_constant__ CUte
             const int k = (t >> 7) * 4;
             float e[4] = {0.f, 0.f, 0.f, 0.f};
             if (t < BM * nslab * 8 && n < p.N) {
+                if (transB && p.vecB && k + 3 < p.K) {      // (N x K) weight: one 16-byte load along k
+                    const float4 q4 = __ldg(reinterpret_cast<const float4*>(p.B + (int64_t)n * p.ldb + k));
+                    e[0] = q4.x; e[1] = q4.y; e[2] = q4.z; e[3] = q4.w;
+                } else {
 #pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    if (k + j < p.K)
-                        e[j] = transB ? __ldg(p.B + (int64_t)n * p.ldb + k + j) : __ldg(p.B + (int64_t)(k + j) * p.ldb + n);
+                    for (int j = 0; j < 4; ++j)
+                        if (k + j < p.K)
+                            e[j] = transB ? __ldg(p.B + (int64_t)n * p.ldb + k + j) : __ldg(p.B + (int64_t)(k + j) * p.ldb + n);
+                }
             }
             bv[u] = make_float4(e[0], e[1], e[2], e[3]);
         }
@@ -129,19 +133,7 @@ node_gemm_kernel(const KParams p, const int transB, const __grid_constant__ CUte
         // ===================== TMA producer =====================
         if (lane == 0) {
             uint32_t it = 0;
-            // The two landing slots keep only 32 KB per SM in flight, far too little to cover DRAM latency at
-            // full bandwidth: the rows of the tiles PF_AHEAD iterations ahead are pulled into L2 meanwhile.
-            for (int a = 0; a < PF_AHEAD; ++a) {
-                const int tp = blockIdx.x + a * gridDim.x;
-                if (tp < ntiles)
-                    for (int ks = 0; ks < nslab; ++ks) tma_prefetch_2d(&map_a, ks * BK, tp * BM);
-            }
             for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
-                {
-                    const int tp = t + PF_AHEAD * gridDim.x;
-                    if (tp < ntiles)
-                        for (int ks = 0; ks < nslab; ++ks) tma_prefetch_2d(&map_a, ks * BK, tp * BM);
-                }
                 for (int ks = 0; ks < nslab; ++ks, ++it) {
                     const uint32_t s = it % NRAW;
                     if (it >= NRAW) mbar_wait(&raw_empty[s], (it / NRAW - 1) & 1);
@@ -312,7 +304,8 @@ int launch_node_gemm(const GemmParams& g, cudaStream_t stream) {
     p.M = g.M; p.N = g.N; p.K = g.K;
     p.A = g.A; p.lda = g.lda; p.B = g.B; p.ldb = g.ldb; p.C = g.C; p.ldc = g.ldc;
     p.alpha = g.alpha; p.beta = g.beta; p.bias = g.bias; p.act = g.act;
-    p.splitk = 1; p.vecA = p.vecB = p.vecC = 1;
+    p.splitk = 1; p.vecA = p.vecC = 1;
+    p.vecB = aligned16(g.B) && (g.ldb % 4 == 0);
     alignas(64) CUtensorMap map_a;
     int rc = make_map_box(&map_a, g.A, g.M, g.K, g.lda, BK, BM);
     if (rc) return rc;
