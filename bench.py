@@ -322,6 +322,26 @@ def b200_main(args):
                       "unit": "GB/s", "frac": a / hbm_peak, "bytes_per_launch": agg_bytes,
                       "note": "C2 activations (54 MB) are L2-resident inside the step; HBM-sized run: "
                               "benchmarks/kernel_bench.py"})
+    sweep_ms, _ = probe_ms("potrf_ext")
+    if sweep_ms:
+        # factor N^3/3 + L^-T through the identity rows N^3/3 + the y row N^2
+        sweep_flop = 2.0 * n ** 3 / 3.0 + float(n) ** 2
+        a = sweep_flop / (sweep_ms * 1e-3) / 1e12
+        extra.append({"kernel": "potrf_ext sweep: %d dependent launches of tgemm_kernel<NT, look-ahead> (largest share "
+                                "of the step)" % ((n + 63) // 64), "bound": "tensor", "achieved": a, "peak": tf_peak,
+                      "unit": "TFLOP/s", "frac": a / tf_peak, "flop_per_call": sweep_flop,
+                      "note": "latency-bound at this size, not throughput-bound: one launch per 64-column panel, each "
+                              "carrying the dependent chain update -> factor next diagonal block -> panel solve "
+                              "(about 25 us of the 38 us per step); DESIGN.md section 4"})
+    nu_ms, nu_cnt = probe_ms("node_update_fwd")
+    if nu_ms:
+        # three of the four layers are 128 -> 128 (persistent TMA-fed kernel), f_in is 117 -> 128
+        nu_bytes = 4.0 * nn_ * (HIDDEN + HIDDEN) + 4.0 * HIDDEN * HIDDEN
+        a = nu_bytes / (nu_ms * 1e-3) / 1e9
+        extra.append({"kernel": "node_update_fwd (tanh(XW+b), average of the four layers)", "bound": "hbm", "achieved": a,
+                      "peak": hbm_peak, "unit": "GB/s", "frac": a / hbm_peak, "bytes_per_launch": nu_bytes,
+                      "note": "C2 activations (54 MB) are L2-resident inside the step; HBM-sized run: "
+                              "benchmarks/kernel_bench.py"})
 
     # ---- end-to-end: host buffers in, loss out, every step (public API) ----
     e2e = None

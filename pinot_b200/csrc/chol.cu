@@ -295,6 +295,14 @@ int64_t outer_block_width(int64_t n) {
     return NB;
 }
 
+bool tc_solve_enabled() {
+    static const bool on = [] {
+        const char* v = getenv("PINOT_B200_SOLVE");
+        return !(v && v[0] == 'f');      // PINOT_B200_SOLVE=ffma selects the CUDA-core panel solve
+    }();
+    return on;
+}
+
 bool lookahead_enabled() {
     static const bool on = [] {
         const char* v = getenv("PINOT_B200_LOOKAHEAD");
@@ -384,7 +392,8 @@ int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, i
         g.post_c0 = (int)c1;
         if (fused) {
             g.post_flag = flags + b1;
-            g.post_solve = 1;
+            // 2: the solve runs on the tensor cores (full 64-column blocks); 1: FFMA version
+            g.post_solve = (tc_solve_enabled() && g.post_nb == NB) ? 2 : 1;
             // the identity rows that enter with block b1 ride along (their update is a no-op) so
             // that tile column 0 solves them too
             g.M = (int)(active_rows_end(c1 + g.post_nb) - c1);

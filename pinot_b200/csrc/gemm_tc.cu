@@ -57,7 +57,13 @@ struct Geo {
     static constexpr int OP_B = KC_PER_STAGE * LBO_B;    // one of B_hi, B_lo
     static constexpr int STAGE = 2 * OP_A + 2 * OP_B;
     static constexpr int PIPE = STAGES * STAGE;
-    static constexpr int DYN_SMEM = (PIPE > DIAG_BYTES ? PIPE : DIAG_BYTES) + 128;
+    // tensor-core panel solve (look-ahead kernel): X tile 128 x 64 and M^T 64 x 64, hi | lo, whole K resident
+    static constexpr int SOLVE_LBO_B = (DIAG_NB / 8) * 128 + 32;
+    static constexpr int SOLVE_A = (DIAG_NB / 4) * LBO_A;          // one of X_hi, X_lo
+    static constexpr int SOLVE_B = (DIAG_NB / 4) * SOLVE_LBO_B;    // one of M_hi, M_lo
+    static constexpr int SOLVE_TC = 2 * SOLVE_A + 2 * SOLVE_B;
+    static constexpr int NEED0 = PIPE > DIAG_BYTES ? PIPE : DIAG_BYTES;
+    static constexpr int DYN_SMEM = (NEED0 > SOLVE_TC ? NEED0 : SOLVE_TC) + 128;
     static constexpr int TMEM_COLS = 2 * BN;             // [0,BN): hi.hi accumulator, [BN,2BN): cross terms
 };
 
@@ -231,6 +237,7 @@ __global__ void __launch_bounds__(NTHREADS, BN == 128 ? 2 : 1) tgemm_kernel(cons
     constexpr int HB = BN / 128;
     extern __shared__ __align__(128) uint8_t dyn_smem[];
     __shared__ __align__(8) uint64_t mma_bar[STAGES];
+    __shared__ __align__(8) uint64_t solve_bar;       // look-ahead kernel: completion of the panel-solve MMAs
     __shared__ uint32_t tmem_base_holder;
 
     const int m0 = blockIdx.y * TM, n0 = blockIdx.x * BN;
@@ -256,6 +263,7 @@ __global__ void __launch_bounds__(NTHREADS, BN == 128 ? 2 : 1) tgemm_kernel(cons
     if (tid == 0) {
 #pragma unroll
         for (int s = 0; s < STAGES; ++s) mbar_init(&mma_bar[s], 1);
+        if (POST) mbar_init(&solve_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
@@ -428,8 +436,10 @@ __global__ void __launch_bounds__(NTHREADS, BN == 128 ? 2 : 1) tgemm_kernel(cons
     }
 
     PB_STAMP(3);
-    // ---- teardown: every warp is done reading TMEM (synchronised above) before warp 0 frees it ----
-    if (warp == 0) {
+    // ---- teardown: every warp is done reading TMEM (synchronised above) before warp 0 frees it; the tiles
+    //      that go on to a tensor-core panel solve keep their columns until that is done ----
+    const bool tc_solve = POST && p.post_wdiag != nullptr && blockIdx.x == 0 && blockIdx.z == 0 && p.post_solve == 2;
+    if (warp == 0 && !tc_solve) {
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)G::TMEM_COLS)
                      : "memory");
     }
@@ -451,7 +461,134 @@ __global__ void __launch_bounds__(NTHREADS, BN == 128 ? 2 : 1) tgemm_kernel(cons
         if (p.post_solve) {
             if (!owner) wait_flag(p.post_flag);
             else __syncthreads();
-            panel_solve_tile(p.C, p.ldc, m0, p.M, p.post_nb, p.post_winv, fsmem);
+            if (POST && p.post_solve == 2) {
+                // ---- panel solve X <- X M on the tensor cores (nb == 64, 16-byte aligned rows) ----
+                // operands: A = this tile's 128 rows of the panel (K = 64), B = M^T (N = 64), both split to
+                // hi / lo over the whole K in the idle pipeline memory; 24 MMAs; the result goes back in place.
+                constexpr int LBOB = G::SOLVE_LBO_B;
+                uint8_t* x_hi = smem;
+                uint8_t* x_lo = smem + G::SOLVE_A;
+                uint8_t* m_hi = smem + 2 * G::SOLVE_A;
+                uint8_t* m_lo = m_hi + G::SOLVE_B;
+                {
+                    float4 xr[8], mr[4];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {          // all loads first: one L2 round trip
+                        const int idx = tid + i * 256;
+                        const int row = idx >> 4, kc = idx & 15;
+                        const int m = m0 + row;
+                        xr[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (m >= p.post_nb && m < p.M)
+                            xr[i] = __ldcg(reinterpret_cast<const float4*>(p.C + (int64_t)m * p.ldc + kc * 4));
+                    }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int idx = tid + i * 256;
+                        const int n = idx & 63, kc = idx >> 6;     // B[n][k] = M[k][n]
+                        const float* src = p.post_winv + (kc * 4) * DIAG_NB + n;
+                        mr[i] = make_float4(__ldcg(src), __ldcg(src + DIAG_NB), __ldcg(src + 2 * DIAG_NB), __ldcg(src + 3 * DIAG_NB));
+                    }
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int idx = tid + i * 256;
+                        const int row = idx >> 4, kc = idx & 15;
+                        float4 h, l;
+                        split_tf32(xr[i].x, h.x, l.x); split_tf32(xr[i].y, h.y, l.y);
+                        split_tf32(xr[i].z, h.z, l.z); split_tf32(xr[i].w, h.w, l.w);
+                        const int off = kc * G::LBO_A + row * 16;
+                        *reinterpret_cast<float4*>(x_hi + off) = h;
+                        *reinterpret_cast<float4*>(x_lo + off) = l;
+                    }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int idx = tid + i * 256;
+                        const int n = idx & 63, kc = idx >> 6;
+                        float4 h, l;
+                        split_tf32(mr[i].x, h.x, l.x); split_tf32(mr[i].y, h.y, l.y);
+                        split_tf32(mr[i].z, h.z, l.z); split_tf32(mr[i].w, h.w, l.w);
+                        const int off = kc * LBOB + n * 16;
+                        *reinterpret_cast<float4*>(m_hi + off) = h;
+                        *reinterpret_cast<float4*>(m_lo + off) = l;
+                    }
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                __syncthreads();
+                if (tid == 0) {
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t id64 = make_idesc(DIAG_NB);
+                    const uint64_t dxa = make_desc(0, G::LBO_A), dmb = make_desc(0, LBOB);
+                    const uint32_t xa = smem_u32(x_hi) >> 4, mb = smem_u32(m_hi) >> 4;
+#pragma unroll
+                    for (int k8 = 0; k8 < DIAG_NB / 8; ++k8) {
+                        const uint64_t a_hi = dxa + (uint64_t)(xa + ((2 * k8 * G::LBO_A) >> 4));
+                        const uint64_t a_lo = a_hi + (uint64_t)(G::SOLVE_A >> 4);
+                        const uint64_t b_hi = dmb + (uint64_t)(mb + ((2 * k8 * LBOB) >> 4));
+                        const uint64_t b_lo = b_hi + (uint64_t)(G::SOLVE_B >> 4);
+                        const uint32_t acc = k8 > 0 ? 1u : 0u;
+                        mma_tf32(tmem_d + BN, a_lo, b_hi, id64, acc);
+                        mma_tf32(tmem_d + BN, a_hi, b_lo, id64, 1u);
+                        mma_tf32(tmem_d, a_hi, b_hi, id64, acc);
+                    }
+                    mma_commit(&solve_bar);
+                }
+                mbar_wait(&solve_bar, 0u);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                {
+                    KParams ps = p;
+                    ps.N = DIAG_NB; ps.beta = 0.f; ps.bias = nullptr; ps.lower = 0; ps.act = 0;
+                    const int c0 = (warp >> 2) * 32;       // warps 0-3: columns 0..31, warps 4-7: 32..63
+                    uint32_t v[32], w[32];
+                    const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)c0;
+                    asm volatile(
+                        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+                        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                        : "r"(taddr)
+                        : "memory");
+                    asm volatile(
+                        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+                        : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]),
+                          "=r"(w[8]), "=r"(w[9]), "=r"(w[10]), "=r"(w[11]), "=r"(w[12]), "=r"(w[13]), "=r"(w[14]), "=r"(w[15]),
+                          "=r"(w[16]), "=r"(w[17]), "=r"(w[18]), "=r"(w[19]), "=r"(w[20]), "=r"(w[21]), "=r"(w[22]), "=r"(w[23]),
+                          "=r"(w[24]), "=r"(w[25]), "=r"(w[26]), "=r"(w[27]), "=r"(w[28]), "=r"(w[29]), "=r"(w[30]), "=r"(w[31])
+                        : "r"(taddr + (uint32_t)BN)
+                        : "memory");
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    // the operands are dead (MMAs complete): the staging tiles may overwrite them, but only once
+                    // every warp has its accumulators in registers
+                    __syncthreads();
+                    float* tile = reinterpret_cast<float*>(smem) + warp * (32 * EPI_LD);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        float4 t;
+                        t.x = __uint_as_float(v[4 * i + 0]) + __uint_as_float(w[4 * i + 0]);
+                        t.y = __uint_as_float(v[4 * i + 1]) + __uint_as_float(w[4 * i + 1]);
+                        t.z = __uint_as_float(v[4 * i + 2]) + __uint_as_float(w[4 * i + 2]);
+                        t.w = __uint_as_float(v[4 * i + 3]) + __uint_as_float(w[4 * i + 3]);
+                        *reinterpret_cast<float4*>(tile + lane * EPI_LD + 4 * i) = t;
+                    }
+                    __syncwarp();
+                    // rows of the diagonal block itself (first 64 rows of tile (0,0)) are not panel rows
+                    if (m0 + q * 32 >= p.post_nb)
+                        epilogue_rows<0>(ps, tile, 1.f, 0.f, 0.f, true, m0, 0, q, c0, lane);
+                }
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                __syncthreads();
+                if (warp == 0) {
+                    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d),
+                                 "r"((uint32_t)G::TMEM_COLS)
+                                 : "memory");
+                }
+            } else {
+                panel_solve_tile(p.C, p.ldc, m0, p.M, p.post_nb, p.post_winv, fsmem);
+            }
             PB_STAMP(7);
         }
     }
