@@ -400,6 +400,22 @@ def b200_main(args):
 
         step_marks = []
 
+        # ... and so is the upload: two captured H2D + index-build graphs (one per staging slot) on the copy stream
+        uploads = None
+        if captured is not None:
+            try:
+                uploads = [pb.CapturedBatchUpload(src_h, dst_h, feat_h, y_h, g_host.number_of_nodes(), bnn, bne,
+                                                  copy_stream, device=dev) for _ in range(2)]
+                mode += " + CUDA-graph replay of the upload (pinot_b200.CapturedBatchUpload)"
+
+                def upload():                              # noqa: F811 - same contract as the eager upload above
+                    u = uploads[n_up[0] % 2]
+                    n_up[0] += 1
+                    return u.replay()
+            except Exception as exc:  # noqa: BLE001
+                sys.stderr.write("bench.py: CUDA-graph capture of the upload failed (%s); eager upload\n" % exc)
+                uploads = None
+
         def e2e_loop(n_steps):
             """Every step uploads its own inputs from pinned host memory and reads its loss back;
             the upload of step k+1 overlaps the compute of step k (two-deep pipeline)."""
@@ -454,6 +470,9 @@ def b200_main(args):
             e2e["captured_step_device_ms"] = pbd.max_over_ranks(sum(ts) / len(ts), dev)
             captured.release()     # the graph holds the NCCL all-reduce: it must go before the process group
             captured = None
+        if uploads is not None:
+            for u in uploads:
+                u.release()
 
     # ---- second headline number of BASELINE.json: exact-GP fit at N = 16 384 (embeddings given):
     #      Gram + sweep (factor, L^-1 y, L^-T) + NLL + closed-form gradients, one GPU ----

@@ -13,7 +13,7 @@ from . import synthetic  # noqa: F401
 from . import active  # noqa: F401
 from . import distributed  # noqa: F401
 from . import captured  # noqa: F401
-from .captured import CapturedTrainStep  # noqa: F401
+from .captured import CapturedTrainStep, CapturedBatchUpload  # noqa: F401
 from .net import Net  # noqa: F401
 from .graph import BatchedGraph, batch, unbatch, sum_nodes  # noqa: F401
 

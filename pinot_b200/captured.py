@@ -96,3 +96,57 @@ class CapturedTrainStep:
             self.graph.reset()
         self.graph = None
         self.loss = None
+
+
+class CapturedBatchUpload:
+    """Host -> device transfer of one batch (edge list, node features, targets, per-graph node counts) plus the
+    graph index build, captured once in a CUDA graph on a copy stream and replayed with one launch per step.
+
+    The pinned HOST tensors given here are the source of every replay: a data loader refills them in place
+    (same numbers of nodes / edges / graphs) and calls ``replay()``, which returns ``(graph, y, event)`` --
+    device-resident, valid once ``event`` has completed, overwritten by the next replay of this object.
+    Use two objects alternately (or copy out with ``CapturedTrainStep.load``) to overlap with compute.
+    One driver call instead of ~25 per batch also takes the upload out of the way of a concurrently
+    running compute graph."""
+
+    def __init__(self, src_h, dst_h, feat_h, y_h, num_nodes, batch_num_nodes, batch_num_edges, stream, device=None):
+        from .graph import BatchedGraph
+        for t in (src_h, dst_h, feat_h, y_h):
+            assert t.is_pinned(), "CapturedBatchUpload needs pinned host tensors"
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.stream = stream
+        self.host = (src_h, dst_h, feat_h, y_h)
+        self.bnn_h = torch.as_tensor(list(batch_num_nodes), dtype=torch.long).pin_memory()
+        self.dev = tuple(torch.empty_like(t, device=dev) for t in self.host) + (torch.empty_like(self.bnn_h, device=dev),)
+        self.meta = (int(num_nodes), list(batch_num_nodes), list(batch_num_edges))
+
+        def body():
+            for d, h in zip(self.dev, self.host + (self.bnn_h,)):
+                d.copy_(h, non_blocking=True)
+            g = BatchedGraph(self.dev[0], self.dev[1], self.meta[0], self.meta[1], self.meta[2], validate=False,
+                             batch_num_nodes_device=self.dev[4])
+            g.ndata["h"] = self.dev[2]
+            g.csr()
+            return g
+
+        cur = torch.cuda.current_stream(dev)
+        stream.wait_stream(cur)
+        with torch.cuda.stream(stream):
+            body()                                  # warm-up outside the capture (lazy initialisation, allocator)
+        stream.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph, stream=stream):
+            self.g = body()
+        self.y = self.dev[3]
+
+    def replay(self):
+        with torch.cuda.stream(self.stream):
+            self.graph.replay()
+            ev = torch.cuda.Event()
+            ev.record(self.stream)
+        return self.g, self.y, ev
+
+    def release(self):
+        torch.cuda.synchronize()
+        self.graph.reset()
+        self.graph = None

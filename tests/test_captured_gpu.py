@@ -60,3 +60,25 @@ def test_load_rejects_a_batch_of_another_size():
     other, yo = synthetic.make_batch(65, seed=2)
     with pytest.raises(ValueError, match="differ in size"):
         step.load(other.to(DEV), yo.to(DEV))
+
+
+def test_captured_upload_replays_follow_the_pinned_host_buffers():
+    g, y = synthetic.make_batch(200, seed=4)
+    s, d = (t.clone().pin_memory() for t in g.edges())
+    feat = g.ndata["h"].clone().pin_memory()
+    yh = y.clone().pin_memory()
+    stream = torch.cuda.Stream()
+    up = pb.CapturedBatchUpload(s, d, feat, yh, g.number_of_nodes(), g.batch_num_nodes().tolist(),
+                                g.batch_num_edges().tolist(), stream)
+    for scale in (1.0, -2.0):
+        feat.copy_(g.ndata["h"] * scale)          # the loader refills the pinned buffers in place
+        yh.copy_(y * scale)
+        gd, yd, ev = up.replay()
+        ev.synchronize()
+        want = g.to(DEV)
+        want.ndata["h"] = want.ndata["h"] * scale
+        assert torch.equal(yd, (y * scale).to(DEV))
+        assert torch.equal(gd.ndata["h"], want.ndata["h"])
+        for name in ("indptr", "indices", "indptr_t", "indices_t", "seg_offsets", "node_seg", "in_norm", "inv_in_deg"):
+            assert torch.equal(getattr(gd.csr(), name), getattr(want.csr(), name)), name
+    up.release()
