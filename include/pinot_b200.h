@@ -145,10 +145,12 @@ PINOT_B200_API int pinot_b200_sgemm_nt_presplit(int64_t M, int64_t N, int64_t K,
  * out[i,j] = K(x_i, y_j) + (i == j) * (diag_add + (diag_add_log ? exp(*diag_add_log) : 0)):
  * the fused `_perturb` (gaussian_process_regressor.py:29-46, rectangular matrices included) and
  * noise term exp(log_sigma) * I (:103-105).
+ * lower_only != 0: 64 x 64 tiles strictly above the main diagonal are skipped (left untouched) -- for a
+ * symmetric matrix that goes straight into the Cholesky sweep, which reads the lower triangle only.
  * --------------------------------------------------------------------------------------------- */
 PINOT_B200_API int pinot_b200_gram_fwd(int kind, const float* x, const float* y, const float* scale,
                         int64_t scale_len, const float* variance, float* out, int64_t ldo, int64_t n,
-                        int64_t n2, int64_t d, float diag_add, const float* diag_add_log,
+                        int64_t n2, int64_t d, float diag_add, const float* diag_add_log, int lower_only,
                         cudaStream_t stream);
 /* Backward of the Gram matrix given dk = dLoss/dK (n x n2).  Outputs (any may be NULL, all are
  * overwritten): dx (n x d), dy (n2 x d), dscale (scale_len), dvariance (1).  symmetric = 1 promises

@@ -36,7 +36,7 @@ SIGNATURES = {
     "pinot_b200_sgemm_nt_tma": [_i64, _i64, _i64, _f32, _ptr, _i64, _ptr, _i64, _f32, _ptr, _i64, _ptr, _i64, _ptr],
     "pinot_b200_tf32_split": [_ptr, _i64, _i64, _i64, _ptr, _i32, _ptr, _ptr, _ptr],
     "pinot_b200_sgemm_nt_presplit": [_i64, _i64, _i64, _f32, _ptr, _ptr, _ptr, _ptr, _f32, _ptr, _i64, _i32, _ptr, _ptr],
-    "pinot_b200_gram_fwd": [_i32, _ptr, _ptr, _ptr, _i64, _ptr, _ptr, _i64, _i64, _i64, _i64, _f32, _ptr, _ptr],
+    "pinot_b200_gram_fwd": [_i32, _ptr, _ptr, _ptr, _i64, _ptr, _ptr, _i64, _i64, _i64, _i64, _f32, _ptr, _i32, _ptr],
     "pinot_b200_gram_bwd": [_i32, _ptr, _ptr, _ptr, _i64, _ptr, _ptr, _i64, _i64, _i64, _i64, _ptr, _ptr, _ptr, _ptr, _i32, _ptr],
     "pinot_b200_potrf_workspace_bytes": [_i64],
     "pinot_b200_potrf_tma_scratch_bytes": [_i64, _i64],

@@ -86,9 +86,10 @@ __global__ void __launch_bounds__(256)
 gram_fwd_kernel(int kind, const float* __restrict__ x, const float* __restrict__ y,
                 const float* __restrict__ scale, int scale_stride, const float* __restrict__ variance,
                 float* __restrict__ out, int64_t ldo, int64_t N, int64_t Np, int D, float diag_add,
-                const float* __restrict__ diag_add_log_dev, int vec_in, int vec_out) {
+                const float* __restrict__ diag_add_log_dev, int vec_in, int vec_out, int lower_only) {
     __shared__ __align__(16) float Xs[FWD_KC * LDS_];
     __shared__ __align__(16) float Ys[FWD_KC * LDS_];
+    if (lower_only && blockIdx.x > blockIdx.y) return;   // tile strictly above the diagonal: the consumer never reads it
     const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
     const int64_t i0 = (int64_t)blockIdx.y * TS, j0 = (int64_t)blockIdx.x * TS;
     float acc[4][4];
@@ -302,7 +303,7 @@ extern "C" {
 
 int pinot_b200_gram_fwd(int kind, const float* x, const float* y, const float* scale,
                         int64_t scale_len, const float* variance, float* out, int64_t ldo, int64_t n,
-                        int64_t n2, int64_t d, float diag_add, const float* diag_add_log,
+                        int64_t n2, int64_t d, float diag_add, const float* diag_add_log, int lower_only,
                         cudaStream_t stream) {
     PB_REQUIRE(kind == 0 || kind == 1, "gram_fwd: kind must be 0 (RBF) or 1 (Matern52)");
     PB_REQUIRE(n >= 0 && n2 >= 0 && d > 0 && d < (1 << 20), "gram_fwd: invalid sizes");
@@ -314,7 +315,7 @@ int pinot_b200_gram_fwd(int kind, const float* x, const float* y, const float* s
     dim3 grid((unsigned)pb::ceil_div(n2, TS), (unsigned)pb::ceil_div(n, TS));
     PB_REQUIRE(grid.y <= 65535, "gram_fwd: too many rows for one launch");
     gram_fwd_kernel<<<grid, 256, 0, stream>>>(kind, x, y, scale, scale_len == 1 ? 0 : 1, variance, out, ldo,
-                                              n, n2, (int)d, diag_add, diag_add_log, vec_in, vec_out);
+                                              n, n2, (int)d, diag_add, diag_add_log, vec_in, vec_out, lower_only ? 1 : 0);
     return pb::check_launch("gram_fwd");
 }
 

@@ -158,15 +158,16 @@ def matmul(a, b, ta=False, tb=False):
 # ------------------------------------------------------------------------------------------------
 # kernel (3): Gram matrix
 # ------------------------------------------------------------------------------------------------
-def gram_raw(kind, x, y, scale, variance, out=None, ldo=None, diag_add=0.0, diag_add_log=None):
-    """Non-differentiable Gram launch; ``out`` may be a view into a larger row-major buffer."""
+def gram_raw(kind, x, y, scale, variance, out=None, ldo=None, diag_add=0.0, diag_add_log=None, lower_only=False):
+    """Non-differentiable Gram launch; ``out`` may be a view into a larger row-major buffer.
+    ``lower_only``: skip the tiles strictly above the diagonal (the sweep reads the lower triangle only)."""
     n, d = x.shape
     n2 = y.shape[0]
     if out is None:
         out = torch.empty((n, n2), device=x.device, dtype=torch.float32)
         ldo = n2
     call("gram_fwd", KIND[kind], ptr(x), ptr(y), ptr(scale), scale.numel(), ptr(variance), ptr(out), ldo, n, n2, d,
-         float(diag_add), ptr(diag_add_log))
+         float(diag_add), ptr(diag_add_log), int(bool(lower_only)))
     return out
 
 
@@ -270,7 +271,7 @@ class _ExactGPLoss(torch.autograd.Function):
         ld = _pad4(n)
         rows = n + 1 + (n if need_grad else 0)
         e = torch.zeros((rows, ld), device=dev, dtype=torch.float32)
-        gram_raw(kind, x, x, sc, var, out=e, ldo=ld, diag_add=EPSILON, diag_add_log=ls)
+        gram_raw(kind, x, x, sc, var, out=e, ldo=ld, diag_add=EPSILON, diag_add_log=ls, lower_only=True)
         e[n, :n] = yv
         if need_grad:
             e[n + 1:, :n].diagonal().fill_(1.0)
@@ -339,7 +340,7 @@ def exact_gp_posterior(x_te, x_tr, y_tr, scale, variance, log_sigma, kind="rbf",
     ls = _f32c(log_sigma.detach().reshape(1))
     ld = _pad4(n)
     e = torch.zeros((n + 1 + nte, ld), device=dev, dtype=torch.float32)
-    gram_raw(kind, x_tr, x_tr, sc, var, out=e, ldo=ld, diag_add=EPSILON, diag_add_log=ls)
+    gram_raw(kind, x_tr, x_tr, sc, var, out=e, ldo=ld, diag_add=EPSILON, diag_add_log=ls, lower_only=True)
     e[n, :n] = _f32c(y_tr.detach().reshape(-1))
     gram_raw(kind, x_te, x_tr, sc, var, out=e[n + 1:], ldo=ld, diag_add=EPSILON)  # rectangular _perturb, :95
     potrf_ext_raw(e, n, n_ext_dense=1 + nte, ext_identity=False, want_diag=False, check=check)
@@ -376,7 +377,8 @@ class ExactGPPosterior:
         ls = _f32c(log_sigma.detach().reshape(1))
         self.ld = ld = _pad4(n)
         e = torch.zeros((2 * n + 1, ld), device=dev, dtype=torch.float32)
-        gram_raw(kind, self.x_tr, self.x_tr, self.scale, self.variance, out=e, ldo=ld, diag_add=EPSILON, diag_add_log=ls)
+        gram_raw(kind, self.x_tr, self.x_tr, self.scale, self.variance, out=e, ldo=ld, diag_add=EPSILON, diag_add_log=ls,
+                 lower_only=True)
         e[n, :n] = _f32c(y_tr.detach().reshape(-1))
         e[n + 1:, :n].diagonal().fill_(1.0)
         potrf_ext_raw(e, n, n_ext_dense=1, ext_identity=True, want_diag=False, check=check)

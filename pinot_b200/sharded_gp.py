@@ -42,7 +42,7 @@ class CudaKernels:
     """The per-rank arithmetic, all through the C-ABI library."""
 
     def gram_block(self, kind, x_rows, x_cols, sc, var, out, ld, ls):
-        ops.gram_raw(kind, x_rows, x_cols, sc, var, out=out, ldo=ld, diag_add=EPSILON, diag_add_log=ls)
+        ops.gram_raw(kind, x_rows, x_cols, sc, var, out=out, ldo=ld, diag_add=EPSILON, diag_add_log=ls, lower_only=True)
 
     def factor_panel(self, blk, w, n_dense, identity):
         """In-place sweep of one panel; returns (diag(L_JJ), info tensor)."""

@@ -34,7 +34,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_loader_and_pure_host_entry_points():
     lib = _lib.load()
-    assert lib.pinot_b200_abi_version() == 2
+    assert lib.pinot_b200_abi_version() == 3
     assert _lib.potrf_workspace_bytes(0) == 0
     # two column blocks: L11 + L11^-T per block, plus the (256-byte rounded) flag array
     assert _lib.potrf_workspace_bytes(65) == 2 * 2 * 64 * 64 * 4 + 256
