@@ -82,7 +82,7 @@ def _problem(n=150, d=6, seed=3):
     return x, y, sc, var, ls
 
 
-def _worker(rank, world, port, out, kind, logdet, cuts):
+def _worker(rank, world, port, out, kind, logdet, cuts, block=32):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     x, y, sc, var, ls = _problem()
@@ -92,7 +92,7 @@ def _worker(rank, world, port, out, kind, logdet, cuts):
     xl = x[r0:r1].clone().requires_grad_(True)
     yl = y[r0:r1].clone().requires_grad_(True)
     sc, var, ls = (t.clone().requires_grad_(True) for t in (sc, var, ls))
-    loss = sharded_gp.sharded_exact_gp_loss(xl, yl, sc, var, ls, kind=kind, exact_logdet=(logdet == "exact"), block=32,
+    loss = sharded_gp.sharded_exact_gp_loss(xl, yl, sc, var, ls, kind=kind, exact_logdet=(logdet == "exact"), block=block,
                                             kernels=OracleKernels())
     (3.0 * loss).sum().backward()
     torch.save({"loss": loss.detach(), "dx": xl.grad, "dy": yl.grad, "dsc": sc.grad, "dvar": var.grad, "dls": ls.grad},
@@ -102,9 +102,13 @@ def _worker(rank, world, port, out, kind, logdet, cuts):
 
 
 def _check(tmp_path, kind, logdet, cuts):
+    _check_custom(tmp_path, kind, logdet, cuts, block=32)
+
+
+def _check_custom(tmp_path, kind, logdet, cuts, block):
     world = len(cuts) - 1
     out = str(tmp_path / "r%d.pt")
-    mp.spawn(_worker, args=(world, _free_port(), out, kind, logdet, cuts), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), out, kind, logdet, cuts, block), nprocs=world, join=True)
     res = [torch.load(out % r) for r in range(world)]
     x, y, sc, var, ls = _problem()
     if kind != "rbf":
@@ -134,6 +138,13 @@ def test_sharded_exact_gp_two_ranks_rbf_trace(tmp_path):
 
 def test_sharded_exact_gp_two_ranks_matern_exact_logdet(tmp_path):
     _check(tmp_path, "matern52", "exact", [0, 90, 150])
+
+
+def test_sharded_exact_gp_three_ranks_one_without_rows_and_one_without_blocks(tmp_path):
+    # 150 rows in blocks of 64 -> 3 column blocks, one per rank; rank 0 contributes no rows at all
+    _check_custom(tmp_path, "rbf", "trace", [0, 0, 80, 150], block=64)
+    # blocks of 96 -> 2 column blocks: rank 2 owns none of the sweep but still owns rows of the gradient
+    _check_custom(tmp_path, "rbf", "exact", [0, 50, 100, 150], block=96)
 
 
 def test_sharded_exact_gp_single_process_matches_oracle():
