@@ -9,7 +9,7 @@
 //               position-preserving, so the split is a flat 16-byte-chunk loop -- and hand the landing slot back
 //               to the producer at once;
 //   warp 1      MMA issuer: 3 tcgen05.mma per k-step (lo.hi + hi.lo -> cross accumulator, hi.hi -> main one)
-//               against the resident pre-split B, tcgen05.commit frees the slab;
+//               against the resident pre-split B, tcgen05.commit frees the operand buffer;
 //   warps 2-9   epilogue: tcgen05.ld (thread = output row, 32 consecutive columns), bias / tanh / beta, 32-byte
 //               stores (st.global.v8: whole L2 sectors) straight from that layout; two warps per TMEM lane quadrant;
 // accumulators double-buffered in TMEM so that the epilogue of row tile t overlaps the MMAs of tile t + 1.
@@ -29,7 +29,7 @@ constexpr int NOP = 2;                              // operand (hi | lo) buffers
 constexpr int SLAB_BYTES = BM * BK * 4;             // 16 KB
 constexpr int MAX_SLABS = 4;                        // K <= 128
 constexpr int B_BYTES = 2 * MAX_SLABS * SLAB_BYTES; // hi | lo, 128 KB
-constexpr int RAW_BYTES = NRAW * SLAB_BYTES;        // 48 KB
+constexpr int RAW_BYTES = NRAW * SLAB_BYTES;        // 32 KB
 constexpr int OP_BYTES = NOP * 2 * SLAB_BYTES;      // per buffer: hi | lo
 constexpr int SMEM_BYTES = B_BYTES + RAW_BYTES + OP_BYTES;   // 224 KB (+ 1 KB static) of the 227 KB a CTA may have
 constexpr int NTHREADS = 448;                       // producer, MMA, 8 epilogue warps, 4 converter warps

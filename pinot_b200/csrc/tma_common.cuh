@@ -35,10 +35,6 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
         "l"(map), "r"(x), "r"(y), "r"(s32(bar))
         : "memory");
 }
-// L2 prefetch of one box of a tiled tensor (no shared-memory destination, no completion to wait for)
-__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* map, int x, int y) {
-    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];" ::"l"(map), "r"(x), "r"(y) : "memory");
-}
 // K-major, SWIZZLE_128B shared-memory matrix descriptor (8 rows x 128 B atoms, SBO = 1024 B).
 __device__ __forceinline__ uint64_t sw128_desc(uint32_t saddr) {
     uint64_t d = 0;
