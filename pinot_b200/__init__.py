@@ -10,6 +10,7 @@ from . import representation  # noqa: F401
 from . import regressors  # noqa: F401
 from . import net  # noqa: F401
 from . import synthetic  # noqa: F401
+from . import data  # noqa: F401
 from . import active  # noqa: F401
 from . import distributed  # noqa: F401
 from . import captured  # noqa: F401
