@@ -87,7 +87,7 @@ class ExactGaussianProcessRegressor(GaussianProcessRegressor):
         k_plus_sigma = k_tr_tr + torch.exp(self.log_sigma) * torch.eye(n, device=k_tr_tr.device)
         # one sweep with right-hand sides [y | I]: L^-1 y and L^-1, hence alpha = L^-T (L^-1 y)
         rhs = torch.cat([y_tr.reshape(n, -1), torch.eye(n, device=k_tr_tr.device)], dim=1)
-        l_low, sol = ops.chol_solve(k_plus_sigma, rhs, check=self.check_positive_definite)
+        l_low, sol = ops.chol_solve(k_plus_sigma, rhs, check=(self.check_positive_definite is True))
         ny = rhs.shape[1] - n
         alpha = ops.matmul(sol[:, ny:], sol[:, :ny], True, False)
         return k_tr_tr, k_te_te, k_te_tr, k_tr_te, l_low, alpha
@@ -242,7 +242,7 @@ class VariationalGaussianProcessRegressor(GaussianProcessRegressor):
         k_tr_tr = self._k_tr_tr()
         k_tr_te = self._k_tr_te(x_te)
         rhs = torch.cat([self.y_tr_mu, self._y_tr_sigma(), k_tr_te], dim=1)
-        l, sol = ops.chol_solve(k_tr_tr, rhs, check=self.check_positive_definite)
+        l, sol = ops.chol_solve(k_tr_tr, rhs, check=(self.check_positive_definite is True))
         return l, sol[:, :1], sol[:, 1:1 + m], sol[:, 1 + m:]
 
     def forward(self, x_te):
@@ -265,7 +265,7 @@ class VariationalGaussianProcessRegressor(GaussianProcessRegressor):
 
     def condition(self, x_te, *args, **kwargs):
         predictive_mean, predictive_cov = self.forward(x_te)
-        scale_tril = ops.cholesky(predictive_cov, check=self.check_positive_definite)
+        scale_tril = ops.cholesky(predictive_cov, check=(self.check_positive_definite is True))
         return torch.distributions.multivariate_normal.MultivariateNormal(
             loc=predictive_mean.flatten(), scale_tril=scale_tril, validate_args=False)
 
@@ -276,7 +276,7 @@ class VariationalGaussianProcessRegressor(GaussianProcessRegressor):
         n = x_te.shape[0]
         m = self.n_inducing_points
         resid = (y_te.flatten() - predictive_mean.flatten()).reshape(n, 1)
-        l_cov, r = ops.chol_solve(predictive_cov, resid, check=self.check_positive_definite)
+        l_cov, r = ops.chol_solve(predictive_cov, resid, check=(self.check_positive_definite is True))
         half_log_det = torch.log(torch.diagonal(l_cov)).sum()
         log_prob = -0.5 * (r * r).sum() - half_log_det - 0.5 * n * math.log(2.0 * math.pi)
         nll = -log_prob  # `.mean()` of a scalar (:473)
