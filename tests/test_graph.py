@@ -4,7 +4,7 @@ import torch
 
 import pinot_b200 as pb
 from pinot_b200 import synthetic
-from pinot_b200.graph import BatchedGraph, GraphCSR
+from pinot_b200.graph import BatchedGraph
 from oracle import dgl_ref
 
 
