@@ -86,3 +86,57 @@ def thompson_sampling_sharded(net, gs_local, global_offset, q=1, generator=None)
         best = vals.argmax(dim=0)
         idx = idxs.gather(0, best[None, :])[0]
     return idx.cpu()
+
+
+# ------------------------------------------------------------------------------------------------
+# greedy acquisition functions over the predictive marginals (pinot/active/acquisition.py:10-69,121-400)
+# ------------------------------------------------------------------------------------------------
+def _top(utility, q):
+    """Indices of the ``q`` largest utilities (all of them if there are fewer), as in ``_greedy`` (:21-27)."""
+    return torch.topk(utility, min(q, len(utility))).indices
+
+
+def temporal(net, gs, y_best=0.0, q=1):
+    """The first ``q`` candidates in data-set order (:29-36, :121-161; baseline for temporal data sets)."""
+    d = _independent(net, gs)
+    n = d.mean.flatten().shape[0]
+    return _top(torch.arange(n - 1, -1, -1, dtype=torch.float32, device=d.mean.device), q)
+
+
+def probability_of_improvement(net, gs, y_best=0.0, q=1):
+    """P(y > y_best) under the predictive marginal (:38-39, :164-201)."""
+    d = _independent(net, gs)
+    # (a float y_best is accepted: recent torch versions insist on a tensor argument to cdf)
+    return _top(1.0 - d.cdf(torch.as_tensor(y_best, dtype=d.mean.dtype, device=d.mean.device)), q)
+
+
+def uncertainty(net, gs, y_best=0.0, q=1):
+    """Predictive variance (:41-42, :204-241)."""
+    return _top(_independent(net, gs).variance, q)
+
+
+def expected_improvement_analytical(net, gs, y_best=0.0, q=1):
+    """Closed-form expected improvement of a normal marginal (:44-53, :244-292)."""
+    d = _independent(net, gs)
+    mu, sigma = d.mean, d.stddev
+    z = (mu - y_best) / sigma
+    unit = torch.distributions.Normal(0, 1)
+    return _top((mu - y_best) * unit.cdf(z) + sigma * torch.exp(unit.log_prob(z)), q)
+
+
+def expected_improvement_monte_carlo(net, gs, y_best=0.0, q=1, n_samples=1000):
+    """Sample mean of max(y - y_best, 0) (:55-59, :295-334)."""
+    d = _independent(net, gs)
+    return _top(torch.nn.functional.relu(d.sample((n_samples,)) - y_best).mean(axis=0), q)
+
+
+def upper_confidence_bound(net, gs, y_best=0.0, q=1, kappa=0.95):
+    """Upper end of the central ``kappa`` interval (:61-64, :337-373; pinot/samplers/utils.py:62-84)."""
+    d = _independent(net, gs)
+    return _top(d.icdf(1 - (1 - torch.tensor(kappa)) / 2), q)
+
+
+def random(net, gs, y_best=0.0, q=1, seed=2666):
+    """Uniform random utilities (:66-67, :376-414; like the reference, ``seed`` is accepted and not used)."""
+    d = _independent(net, gs)
+    return _top(torch.rand(d.batch_shape), q)
