@@ -188,6 +188,9 @@ node_gemm_kernel(const KParams p, const int transB, const __grid_constant__ CUte
                     const float4 v = *reinterpret_cast<const float4*>(raw + (i * 128 + ct) * 16);
                     split4(v, h[i], l[i]);
                 }
+                // The slot was read through the generic proxy and will be rewritten by TMA (async proxy): without
+                // this fence the refill can overtake the reads (seen as 1e-2 errors with two converter groups).
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 mbar_arrive(&raw_empty[s]);                      // the landing slot may be refilled
                 const uint32_t o = it % NOP;
                 if (it >= NOP) mbar_wait(&op_empty[o], (it / NOP - 1) & 1);   // the MMAs that read this buffer are done
