@@ -3,11 +3,18 @@
     python bench.py --gpus N --steps K --warmup W            # the B200 path (one process per GPU)
     python bench.py --impl reference --steps K --warmup W    # the reference's CPU arithmetic (oracle port)
 
-Workload (BASELINE.json configs[1], SURVEY.md section 8d "C2"): 4 200 synthetic molecules per GPU
-(~25 atoms / ~54 directed edges each), GraphConv 3x128 + tanh, sum readout, exact GP with pinot's
+Headline workload (BASELINE.json configs[1], SURVEY.md section 8d "C2"): 4 200 synthetic molecules per
+GPU (~25 atoms / ~54 directed edges each), GraphConv 3x128 + tanh, sum readout, exact GP with pinot's
 RBF kernel, full-batch objective; one step = zero_grad -> Net.loss -> backward -> (gradient
 all-reduce when N > 1) -> Adam.step, as in pinot/app/experiment.py:78-89.  Weak scaling: every rank
 trains on its own 4 200-molecule batch and the ranks exchange ONE flat gradient all-reduce per step.
+
+Extra keys on the same JSON line (none of them changes `value`):
+  c1_esol_shape        the same step at configs[0] (1 128 molecules: north_star's ">= 50x" shape), device-timed
+                       and end to end, with the CPU port at 1 128 molecules beside it (N = 1 only)
+  exact_gp_fit_n16k    second headline metric: exact-GP fit ms at N = 16 384, with its CPU baseline (N = 1 only)
+  sharded_gp_fit       the same fit with Gram + Cholesky sweep sharded over the N ranks (N = 16 384 and 65 536)
+  bo_round             one Thompson-sampling acquisition round over the 1 M-molecule pool split over the N ranks
 """
 import argparse
 import json
@@ -25,9 +32,12 @@ if ROOT not in sys.path:
 METRIC = "molecules/sec (GCN+GP train step)"
 UNIT = "molecules/s"
 CONFIG = [128, "tanh", 128, "tanh", 128, "tanh"]
-N_MOL = 4200
+N_MOL = 4200          # configs[1] (C2)
+N_MOL_C1 = 1128       # configs[0] (C1, ESOL shape)
 HIDDEN = 128
 KERNEL_SCALE = -3.0  # "trained-like" length-scale: at init K is numerically the identity
+POOL_CHUNKS = 8       # the 1 M-molecule pool is generated as 8 chunks of 125 000 (seeds 100..107)
+POOL_CHUNK = 125000
 
 
 def parse():
@@ -40,24 +50,40 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-fit16k", action="store_true")
+    ap.add_argument("--no-c1", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip sharded_gp_fit and bo_round")
+    ap.add_argument("--pool-chunk", type=int, default=POOL_CHUNK, help="molecules per pool chunk (8 chunks)")
+    ap.add_argument("--cpu-budget-s", type=float, default=200.0, help="wall-clock budget of the reference arm")
     return ap.parse_args()
+
+
+def profile_json(name):
+    """A committed evidence file under profiles/ (latest round first), or {}."""
+    for rnd in ("r02", "r01"):
+        path = os.path.join(ROOT, "profiles", rnd, name)
+        try:
+            with open(path) as f:
+                d = json.load(f)
+            d["_file"] = "profiles/%s/%s" % (rnd, name)
+            return d
+        except (OSError, ValueError):
+            continue
+    return {}
 
 
 def ncu_traffic(kernel_key):
     """DRAM bytes (read + write) per launch of a kernel from the committed ncu --set full capture
-    (profiles/r01/ncu_traffic.json, taken at the default workload), or None."""
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01", "ncu_traffic.json")
+    (profiles/rNN/ncu_traffic.json, taken at the default workload), or None."""
     try:
-        with open(path) as f:
-            return float(json.load(f)["kernels"][kernel_key]["dram_bytes_per_launch"])
-    except (OSError, KeyError, ValueError):
+        return float(profile_json("ncu_traffic.json")["kernels"][kernel_key]["dram_bytes_per_launch"])
+    except (KeyError, ValueError, TypeError):
         return None
 
 
-def workload_config(n_mol, world):
+def workload_config(n_mol, world, label="C2"):
     return {
-        "workload": "C2: %d synthetic molecules per GPU (25 atoms / 54 directed edges), GraphConv 3x128 + "
-                    "exact GP (RBF), full-batch marginal likelihood, Adam" % n_mol,
+        "workload": "%s: %d synthetic molecules per GPU (25 atoms / 54 directed edges), GraphConv 3x128 + "
+                    "exact GP (RBF), full-batch marginal likelihood, Adam" % (label, n_mol),
         "molecules_per_gpu": n_mol, "global_molecules": n_mol * world, "hidden": HIDDEN,
         "kernel_scale_init": KERNEL_SCALE, "parallelism": "dp%d (gradient all-reduce)" % world,
         "l2": "flushed between timed steps (256 MiB write)",
@@ -65,63 +91,13 @@ def workload_config(n_mol, world):
     }
 
 
-# --------------------------------------------------------------------------------------------------
-# CPU arm: the oracle's restatement of the reference arithmetic (the reference itself needs DGL and
-# is not present on the GPU box)
-# --------------------------------------------------------------------------------------------------
-def cpu_arm(n_mol, steps, warmup, seed=2666, budget_s=170.0):
-    """Times zero_grad -> loss -> backward -> Adam.step of the reference arithmetic on the host
-    cores.  Returns (molecules/s, ms_per_step, cores, sample description)."""
-    from oracle import net_ref
-    from pinot_b200 import synthetic
-    import psutil
-
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-
-    def build(n):
-        g, y = synthetic.make_batch(n, seed=seed)
-        s, d = g.edges()
-        rg = net_ref.graph_from_arrays(s, d, g.number_of_nodes(), g.batch_num_nodes().tolist(),
-                                       g.batch_num_edges().tolist(), g.ndata["h"])
-        torch.manual_seed(0)
-        params = init_state(HIDDEN)
-        p = {k: v.clone().requires_grad_(True) for k, v in params.items()}
-        opt = torch.optim.Adam(list(p.values()), 1e-3)
-        return rg, y, p, opt
-
-    def step(rg, y, p, opt):
-        opt.zero_grad()
-        loss, _ = net_ref.exact_net_loss(rg, y, p, CONFIG)
-        loss.sum().backward()
-        opt.step()
-        return float(loss.sum())
-
-    # the reference materialises an (N, N, 128) fp32 tensor several times over (forward, norm,
-    # backward): ~9 GB per copy at N = 4200
-    avail = psutil.virtual_memory().available / 2 ** 30
-    n = n_mol if avail > 110 else min(n_mol, 1128)
-    rg, y, p, opt = build(n)
-    t0 = time.perf_counter()
-    step(rg, y, p, opt)
-    first = time.perf_counter() - t0
-    done_warm = 1
-    if n > 1128 and first * (steps + max(warmup - 1, 0)) > budget_s:
-        n = 1128
-        rg, y, p, opt = build(n)
-        done_warm = 0
-    for _ in range(max(warmup - done_warm, 0)):
-        step(rg, y, p, opt)
-    times = []
-    for _ in range(steps):
-        t0 = time.perf_counter()
-        step(rg, y, p, opt)
-        times.append(time.perf_counter() - t0)
-    ms = 1e3 * sum(times) / len(times)
-    sample = ("%d of the %d molecules per step (same generator and seed), %d timed steps after %d warm-up, "
-              "torch CPU fp32 with %d threads; oracle port of the reference arithmetic (N x N x D broadcast "
-              "distance, torch Cholesky, autograd)" % (n, n_mol, steps, warmup, cores))
-    return n / (ms * 1e-3), ms, cores, sample
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return p.get("hbm_gbs", 6650.0), p.get("bf16_tflops_sustained", 1400.0), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, 1400.0, "fallback (B200_PROFILING.md)"
 
 
 def init_state(hidden):
@@ -134,18 +110,127 @@ def init_state(hidden):
     return {k: v.detach().clone() for k, v in net.state_dict().items()}
 
 
+# --------------------------------------------------------------------------------------------------
+# CPU arm: the oracle's restatement of the reference arithmetic (the reference itself needs DGL and
+# is not present on the GPU box)
+# --------------------------------------------------------------------------------------------------
+def cpu_arm(n_mol, steps, warmup, seed=2666, budget_s=200.0):
+    """Times zero_grad -> loss -> backward -> Adam.step of the reference arithmetic on the host cores
+    at EXACTLY ``n_mol`` molecules whenever the host has the memory for it; the number of timed steps
+    is cut to what fits ``budget_s`` (never the workload).  Returns a dict."""
+    from oracle import net_ref
+    from pinot_b200 import synthetic
+    import psutil
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    # the reference materialises an (N, N, 128) fp32 tensor several times over (forward, norm,
+    # backward): N^2 * 512 B per copy, about nine copies alive at the peak of the backward pass
+    need_gib = 9.0 * n_mol * n_mol * 512 / 2 ** 30
+    avail_gib = psutil.virtual_memory().available / 2 ** 30
+    n = n_mol
+    shrunk = None
+    if need_gib > 0.9 * avail_gib:
+        n = max(64, int((0.9 * avail_gib * 2 ** 30 / (9.0 * 512)) ** 0.5))
+        shrunk = "host memory: %.0f GiB available, the reference arithmetic needs ~%.0f GiB at %d molecules" % (
+            avail_gib, need_gib, n_mol)
+    g, y = synthetic.make_batch(n, seed=seed)
+    s, d = g.edges()
+    rg = net_ref.graph_from_arrays(s, d, g.number_of_nodes(), g.batch_num_nodes().tolist(),
+                                   g.batch_num_edges().tolist(), g.ndata["h"])
+    torch.manual_seed(0)
+    p = {k: v.clone().requires_grad_(True) for k, v in init_state(HIDDEN).items()}
+    opt = torch.optim.Adam(list(p.values()), 1e-3)
+
+    def step():
+        opt.zero_grad()
+        loss, _ = net_ref.exact_net_loss(rg, y, p, CONFIG)
+        loss.sum().backward()
+        opt.step()
+        return float(loss.detach().sum())
+
+    t0 = time.perf_counter()
+    step()
+    first = time.perf_counter() - t0
+    warm_done = 1
+    # steps that fit the budget (at least 3 timed); extra warm-up only if it is cheap
+    while warm_done < warmup and first * (warm_done + 1 + steps) <= budget_s:
+        step()
+        warm_done += 1
+    timed = steps
+    if first * (warm_done + steps) > budget_s:
+        timed = max(3, min(steps, int(budget_s / first) - warm_done))
+    times = []
+    for _ in range(timed):
+        t0 = time.perf_counter()
+        step()
+        times.append(time.perf_counter() - t0)
+    ms = 1e3 * sum(times) / len(times)
+    sample = ("%d molecules per step (the GPU arm's generator and seed), %d timed steps after %d warm-up "
+              "(requested %d / %d; cut to a %.0f s budget, the workload is never cut for time), torch CPU fp32 with %d "
+              "threads; oracle port of the reference arithmetic (N x N x D broadcast distance, torch Cholesky, "
+              "autograd)" % (n, timed, warm_done, steps, warmup, budget_s, cores))
+    if shrunk:
+        sample += "; SHRUNK from %d molecules: %s" % (n_mol, shrunk)
+    return {"value": n / (ms * 1e-3), "ms_per_step": ms, "cores": cores, "sample": sample, "molecules": n,
+            "steps": timed, "warmup": warm_done}
+
+
+def cpu_fit_baseline(n16=16384, d=HIDDEN, sample_chunks=4, chunk=256):
+    """CPU baseline of the exact-GP fit (loss + all gradients, embeddings given):
+    (i) the oracle's op-for-op port of the reference (it materialises N x N x D) at the largest N
+    that fits the host, one run; (ii) the row-chunked restatement at N = 16 384, where the Gram
+    forward/backward is timed on ``sample_chunks`` row chunks of ``chunk`` rows and scaled to all 64
+    (every chunk costs the same) and the factorisation + its autograd backward are timed in full."""
+    from oracle import gp_ref
+    import psutil
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    gen = torch.Generator().manual_seed(0)
+    x = 0.1 * torch.randn(n16, d, generator=gen)
+    y = torch.randn(n16, 1, generator=gen)
+    sc, var, ls = torch.zeros(d), torch.zeros(()), torch.tensor(-3.0)
+    out = {"cores": cores, "kind": "port"}
+    # (i) unchunked port at the largest power-of-two N whose ~6 live copies of N^2 D floats fit
+    avail = psutil.virtual_memory().available
+    n_fit = 4096
+    while n_fit > 512 and 6.0 * n_fit * n_fit * d * 4 > 0.8 * avail:
+        n_fit //= 2
+    ts = [t.clone().requires_grad_(True) for t in (x[:n_fit], y[:n_fit], sc, var, ls)]
+    t0 = time.perf_counter()
+    gp_ref.exact_gp_loss(*ts).sum().backward()
+    out["unchunked_port"] = {"n": n_fit, "ms": 1e3 * (time.perf_counter() - t0),
+                             "what": "oracle port of the reference (N x N x D distance tensor, autograd), one run"}
+    del ts
+    # (ii) row-chunked restatement at the full size
+    tm = {}
+    gp_ref.exact_gp_fit_chunked(x, y, sc, var, ls, chunk=chunk, sample_chunks=sample_chunks, timings=tm)
+    scale_up = tm["gram_chunks_total"] / tm["gram_chunks_timed"]
+    est = 1e3 * (tm["gram_fwd_s"] * scale_up + tm["gram_fwd_bwd_s"] * scale_up + tm["factor_and_backward_s"])
+    out.update({
+        "value": est, "unit": "ms", "n": n16,
+        "sample": "row-chunked restatement (oracle.gp_ref.exact_gp_fit_chunked): Gram forward and forward+backward "
+                  "timed on %d of %d chunks of %d rows and scaled x%.0f, Cholesky + solves + autograd backward timed "
+                  "in full at N = %d; %d threads" % (tm["gram_chunks_timed"], tm["gram_chunks_total"], chunk, scale_up,
+                                                      n16, cores),
+        "phases_s": {k: v for k, v in tm.items() if k.endswith("_s")},
+    })
+    return out
+
+
 def reference_main(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    value, ms, cores, sample = cpu_arm(args.molecules, args.steps, args.warmup)
+    r = cpu_arm(args.molecules, args.steps, args.warmup, budget_s=args.cpu_budget_s)
+    cfg = workload_config(r["molecules"], 1, "C2" if r["molecules"] == N_MOL else "custom")
     line = {
-        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args.molecules, 1),
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
-        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": r["steps"], "warmup": r["warmup"], "steps_requested": args.steps, "warmup_requested": args.warmup,
+        "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
+        "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]},
+        "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line))
@@ -200,28 +285,42 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def measured_peaks():
-    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(path):
-        with open(path) as f:
-            p = json.load(f)
-        return p.get("hbm_gbs", 6650.0), p.get("bf16_tflops_sustained", 1400.0), "measured (MEASURED_PEAKS.json)"
-    return 6650.0, 1400.0, "fallback (B200_PROFILING.md)"
+PROBES = ["gp_nll_grad", "mp_csr_aggregate_fwd", "mp_csr_aggregate_bwd", "potrf_ext", "gram_fwd", "gram_bwd",
+          "node_update_fwd", "node_update_bwd", "segment_readout_fwd", "segment_readout_bwd", "gemv_rows", "gp_nll",
+          "trtri_lower", "sgemm"]
 
 
-def b200_main(args):
+class Ctx:
+    """Per-process state shared by the measurements."""
+
+    def __init__(self):
+        from pinot_b200 import _lib, distributed as pbd
+        self.rank, self.world, self.local_rank = pbd.init_from_env()
+        assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
+        self.dev = torch.device("cuda", self.local_rank)
+        torch.cuda.set_device(self.dev)
+        _lib.load()
+        self.flush_buf = torch.empty(64 * 2 ** 20, dtype=torch.float32, device=self.dev)  # 256 MiB > 126 MB L2
+
+    def barrier(self):
+        if self.world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(self, v):
+        from pinot_b200 import distributed as pbd
+        return pbd.max_over_ranks(v, self.dev)
+
+
+def measure_train_step(ctx, n_mol, steps, warmup, want_e2e, sample_clocks):
+    """Device-timed steps with resident inputs, then (optionally) the end-to-end loop from pinned host
+    buffers through the public API.  Returns a dict of raw measurements."""
     import pinot_b200 as pb
     from pinot_b200 import _lib, distributed as pbd, synthetic
     from pinot_b200.graph import BatchedGraph
 
-    rank, world, local_rank = pbd.init_from_env()
-    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
-    dev = torch.device("cuda", local_rank)
-    torch.cuda.set_device(dev)
-    _lib.load()
-    n_mol = args.molecules
-
-    # ---- workload: this rank's batch, resident in HBM ----
+    rank, world, dev = ctx.rank, ctx.world, ctx.dev
+    flush_buf = ctx.flush_buf
     g_host, y_host = synthetic.make_batch(n_mol, seed=2666 + rank)
     g = g_host.to(dev)
     y = y_host.to(dev)
@@ -237,7 +336,6 @@ def b200_main(args):
     pbd.broadcast_parameters(net)
     opt = torch.optim.Adam(net.parameters(), 1e-3)
     bucket = pbd.GradientBucket(net.parameters())
-    flush_buf = torch.empty(64 * 2 ** 20, dtype=torch.float32, device=dev)  # 256 MiB > 126 MB L2
 
     def step(graph, target):
         opt.zero_grad(set_to_none=True)
@@ -247,281 +345,397 @@ def b200_main(args):
         opt.step()
         return loss
 
-    def barrier():
-        if world > 1:
-            torch.distributed.barrier()
-        torch.cuda.synchronize()
-
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
+    sampler = ClockSampler(ctx.local_rank)
+    if sample_clocks and rank == 0:
         sampler.start()
-    for _ in range(max(args.warmup, 3)):
+    for _ in range(max(warmup, 3)):
         step(g, y)
-    barrier()
+    ctx.barrier()
 
-    probe_names = ["gp_nll_grad", "mp_csr_aggregate_fwd", "mp_csr_aggregate_bwd", "potrf_ext", "gram_fwd", "gram_bwd",
-                   "node_update_fwd", "node_update_bwd", "segment_readout_fwd"]
-    _lib.probe = {k: [] for k in probe_names}
+    _lib.probe = {k: [] for k in PROBES}
     launches0 = _lib.launch_count()
     evs = []
-    barrier()
-    for _ in range(args.steps):
+    ctx.barrier()
+    for _ in range(steps):
         flush_buf.zero_()
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         s.record()
         loss = step(g, y)
         e.record()
         evs.append((s, e))
-    barrier()
+    ctx.barrier()
     net.output_regressor.verify()
     launches = _lib.launch_count() - launches0
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop() if (sample_clocks and rank == 0) else None
     probes, _lib.probe = _lib.probe, None
     step_ms = [s.elapsed_time(e) for s, e in evs]
-    total_ms = pbd.max_over_ranks(sum(step_ms), dev)
-    ms_per_step = total_ms / args.steps
-    value = n_mol * world / (ms_per_step * 1e-3)
-    final_loss = float(loss.detach())
+    ms_per_step = ctx.max_over_ranks(sum(step_ms)) / steps
+    res = {"n_mol": n_mol, "ms_per_step": ms_per_step, "value": n_mol * world / (ms_per_step * 1e-3),
+           "launches": launches, "clocks": clocks, "final_loss": float(loss.detach()),
+           "nodes": g.number_of_nodes(), "edges": g.number_of_edges(), "shares": {}, "e2e": None}
     del loss   # no live autograd graph: the CUDA-graph capture below needs fresh AccumulateGrad nodes
-
-    # ---- per-kernel timings from the probes (CUDA events on the launching stream, timed region) ----
-    def probe_ms(name):
-        ev = probes.get(name, [])
-        return (sum(s.elapsed_time(e) for s, e in ev) / len(ev), len(ev)) if ev else (None, 0)
-
-    hbm_peak, tf_peak, peak_src = measured_peaks()
-    nn_, ne_ = g.number_of_nodes(), g.number_of_edges()
-    shares = {}
-    for k in probe_names:
-        ms, cnt = probe_ms(k)
-        if ms is not None:
-            shares[k] = {"ms_per_call": ms, "calls_per_step": cnt / args.steps,
-                         "share_of_step": ms * cnt / args.steps / ms_per_step}
-    grad_ms, _ = probe_ms("gp_nll_grad")
-    n = n_mol
-    grad_flop = n ** 3 / 3.0  # L^-T diag(L) L^-1, both factors triangular, symmetric result
-    roofline = {
-        "kernel": "tgemm_tma_kernel (TMA-fed tcgen05 3xTF32, persistent) in pinot_b200_gp_nll_grad: closed-form "
-                  "marginal-likelihood gradient 0.5 L^-T diag(L) L^-1 - 0.5 alpha alpha^T, N=%d; the timed span "
-                  "is the whole C-ABI call (hi/lo split pass + GEMM)" % n,
-        "bound": "tensor", "achieved": grad_flop / (grad_ms * 1e-3) / 1e12 if grad_ms else None,
-        "peak": tf_peak, "unit": "TFLOP/s", "peak_source": peak_src + ", bf16 sustained",
-        "traffic": ncu_traffic("tgemm_tma_kernel") if n == 4200 else None,
-        "note": "algorithmic flops N^3/3 (triangular x triangular, symmetric output); the fp32-parity path "
-                "issues 3 TF32 MMAs per product, so the tensor pipe executes 3x these flops at the TF32 rate "
-                "(half the bf16 peak used as denominator): frac = 1/6 would be a saturated TF32 pipe",
-    }
-    if roofline["achieved"] is not None:
-        roofline["frac"] = roofline["achieved"] / tf_peak
-    agg_ms, _ = probe_ms("mp_csr_aggregate_fwd")
-    agg_bytes = 4.0 * HIDDEN * nn_ * 2 + 4.0 * ne_ + 4.0 * (nn_ + 1) + 8.0 * nn_
-    extra = []
-    if agg_ms:
-        a = agg_bytes / (agg_ms * 1e-3) / 1e9
-        extra.append({"kernel": "mp_aggregate_kernel<4> (fwd)", "bound": "hbm", "achieved": a, "peak": hbm_peak,
-                      "unit": "GB/s", "frac": a / hbm_peak, "bytes_per_launch": agg_bytes,
-                      "note": "C2 activations (54 MB) are L2-resident inside the step; HBM-sized run: "
-                              "benchmarks/kernel_bench.py"})
-    sweep_ms, _ = probe_ms("potrf_ext")
-    if sweep_ms:
-        # factor N^3/3 + L^-T through the identity rows N^3/3 + the y row N^2
-        sweep_flop = 2.0 * n ** 3 / 3.0 + float(n) ** 2
-        a = sweep_flop / (sweep_ms * 1e-3) / 1e12
-        extra.append({"kernel": "potrf_ext sweep: %d dependent launches of tgemm_kernel<NT, look-ahead> (largest share "
-                                "of the step)" % ((n + 63) // 64), "bound": "tensor", "achieved": a, "peak": tf_peak,
-                      "unit": "TFLOP/s", "frac": a / tf_peak, "flop_per_call": sweep_flop,
-                      "note": "latency-bound at this size, not throughput-bound: one launch per 64-column panel, each "
-                              "carrying the dependent chain update -> factor next diagonal block -> panel solve "
-                              "(about 25 us of the 38 us per step); DESIGN.md section 4"})
-    nu_ms, nu_cnt = probe_ms("node_update_fwd")
-    if nu_ms:
-        # three of the four layers are 128 -> 128 (persistent TMA-fed kernel), f_in is 117 -> 128
-        nu_bytes = 4.0 * nn_ * (HIDDEN + HIDDEN) + 4.0 * HIDDEN * HIDDEN
-        a = nu_bytes / (nu_ms * 1e-3) / 1e9
-        extra.append({"kernel": "node_update_fwd (tanh(XW+b), average of the four layers)", "bound": "hbm", "achieved": a,
-                      "peak": hbm_peak, "unit": "GB/s", "frac": a / hbm_peak, "bytes_per_launch": nu_bytes,
-                      "note": "C2 activations (54 MB) are L2-resident inside the step; HBM-sized run: "
-                              "benchmarks/kernel_bench.py"})
+    for k in PROBES:
+        ev = probes.get(k, [])
+        if ev:
+            ms = sum(s.elapsed_time(e) for s, e in ev) / len(ev)
+            res["shares"][k] = {"ms_per_call": ms, "calls_per_step": len(ev) / steps,
+                                "share_of_step": ms * len(ev) / steps / ms_per_step}
+    if not want_e2e:
+        return res
 
     # ---- end-to-end: host buffers in, loss out, every step (public API) ----
-    e2e = None
-    if not args.no_e2e:
-        src_h, dst_h = (t.pin_memory() for t in g_host.edges())
-        feat_h = g_host.ndata["h"].pin_memory()
-        y_h = y_host.pin_memory()
-        bnn, bne = g_host.batch_num_nodes().tolist(), g_host.batch_num_edges().tolist()
-        h2d = sum(t.numel() * t.element_size() for t in (src_h, dst_h, feat_h, y_h)) + 8 * len(bnn)
+    src_h, dst_h = (t.pin_memory() for t in g_host.edges())
+    feat_h = g_host.ndata["h"].pin_memory()
+    y_h = y_host.pin_memory()
+    bnn, bne = g_host.batch_num_nodes().tolist(), g_host.batch_num_edges().tolist()
+    h2d = sum(t.numel() * t.element_size() for t in (src_h, dst_h, feat_h, y_h)) + 8 * len(bnn)
+    copy_stream = torch.cuda.Stream(device=dev, priority=-1)   # its small kernels go ahead of the step's
+    bnn_h = g_host.batch_num_nodes().to(torch.long).pin_memory()
+    stage = [tuple(torch.empty_like(t, device=dev) for t in (src_h, dst_h, feat_h, y_h, bnn_h)) for _ in range(2)]
+    n_up = [0]
 
-        copy_stream = torch.cuda.Stream(device=dev, priority=-1)   # its small kernels go ahead of the step's
-        # two staging slots on the device, reused every other step (no per-step large allocations)
-        bnn_h = g_host.batch_num_nodes().to(torch.long).pin_memory()
-        stage = [tuple(torch.empty_like(t, device=dev) for t in (src_h, dst_h, feat_h, y_h, bnn_h)) for _ in range(2)]
-        n_up = [0]
+    def upload_eager():
+        """H2D of one step's inputs + graph index build, on the copy stream."""
+        s_d, d_d, f_d, y_d, b_d = stage[n_up[0] % 2]
+        n_up[0] += 1
+        with torch.cuda.stream(copy_stream):
+            for dst_t, src_t in ((s_d, src_h), (d_d, dst_h), (f_d, feat_h), (y_d, y_h), (b_d, bnn_h)):
+                dst_t.copy_(src_t, non_blocking=True)
+            gs = BatchedGraph(s_d, d_d, g_host.number_of_nodes(), bnn, bne, validate=False, batch_num_nodes_device=b_d)
+            gs.ndata["h"] = f_d
+            gs.csr()
+            ev = torch.cuda.Event()
+            ev.record(copy_stream)
+        return gs, y_d, ev
 
-        def upload():
-            """H2D of one step's inputs + graph index build, on the copy stream."""
-            s_d, d_d, f_d, y_d, b_d = stage[n_up[0] % 2]
-            n_up[0] += 1
-            t_ = [time.perf_counter()]
-            with torch.cuda.stream(copy_stream):
-                s_d.copy_(src_h, non_blocking=True)
-                d_d.copy_(dst_h, non_blocking=True)
-                f_d.copy_(feat_h, non_blocking=True)
-                y_d.copy_(y_h, non_blocking=True)
-                b_d.copy_(bnn_h, non_blocking=True)
-                t_.append(time.perf_counter())
-                gs = BatchedGraph(s_d, d_d, g_host.number_of_nodes(), bnn, bne, validate=False,
-                                  batch_num_nodes_device=b_d)
-                gs.ndata["h"] = f_d
-                t_.append(time.perf_counter())
-                gs.csr()
-                t_.append(time.perf_counter())
-                ev = torch.cuda.Event()
-                ev.record(copy_stream)
-            if os.environ.get("PINOT_B200_BENCH_DEBUG") and t_[-1] - t_[0] > 6e-3:
-                sys.stderr.write("slow upload: copies %.2f ms, graph %.2f ms, csr %.2f ms\n" % tuple(
-                    1e3 * (b - a) for a, b in zip(t_[:-1], t_[1:])))
-            return gs, y_d, ev
-
-        # The step itself is replayed from a CUDA graph (pinot_b200.CapturedTrainStep, the public API for
-        # full-batch training): one launch call per step instead of ~150, so the host's only per-step work
-        # is the upload of the next batch.  Falls back to the eager step if the capture is refused.
-        captured, mode = None, "eager step"
+    upload = upload_eager
+    # The step itself is replayed from a CUDA graph (pinot_b200.CapturedTrainStep, the public API for
+    # full-batch training): one launch call per step instead of ~150, so the host's only per-step work
+    # is the upload of the next batch.  Falls back to the eager step if the capture is refused.
+    captured, uploads, mode = None, None, "eager step"
+    try:
+        opt_c = torch.optim.Adam(net.parameters(), 1e-3, capturable=True)
+        g_static = g_host.to(dev)
+        g_static.csr()
+        captured = pb.CapturedTrainStep(net, opt_c, g_static, y_host.to(dev),
+                                        after_backward=lambda: bucket.allreduce(average=False))
+        mode = "CUDA-graph replay of the step (pinot_b200.CapturedTrainStep)"
+    except Exception as exc:  # noqa: BLE001 - any capture failure means: measure the eager path
+        sys.stderr.write("bench.py: CUDA-graph capture of the step failed (%s); e2e uses the eager step\n" % exc)
+        captured = None
+    if captured is not None:
+        # ... and so is the upload: two captured H2D + index-build graphs (one per staging slot)
         try:
-            opt_c = torch.optim.Adam(net.parameters(), 1e-3, capturable=True)
-            g_static = g_host.to(dev)
-            g_static.csr()
-            captured = pb.CapturedTrainStep(net, opt_c, g_static, y_host.to(dev),
-                                            after_backward=lambda: bucket.allreduce(average=False))
-            mode = "CUDA-graph replay of the step (pinot_b200.CapturedTrainStep)"
-        except Exception as exc:  # noqa: BLE001 - any capture failure means: measure the eager path
-            sys.stderr.write("bench.py: CUDA-graph capture of the step failed (%s); e2e uses the eager step\n" % exc)
-            captured = None
+            uploads = [pb.CapturedBatchUpload(src_h, dst_h, feat_h, y_h, g_host.number_of_nodes(), bnn, bne,
+                                              copy_stream, device=dev) for _ in range(2)]
+            mode += " + CUDA-graph replay of the upload (pinot_b200.CapturedBatchUpload)"
 
-        step_marks = []
+            def upload():
+                u = uploads[n_up[0] % 2]
+                n_up[0] += 1
+                return u.replay()
+        except Exception as exc:  # noqa: BLE001
+            sys.stderr.write("bench.py: CUDA-graph capture of the upload failed (%s); eager upload\n" % exc)
+            uploads, upload = None, upload_eager
+    step_marks = []
 
-        # ... and so is the upload: two captured H2D + index-build graphs (one per staging slot) on the copy stream
-        uploads = None
-        if captured is not None:
-            try:
-                uploads = [pb.CapturedBatchUpload(src_h, dst_h, feat_h, y_h, g_host.number_of_nodes(), bnn, bne,
-                                                  copy_stream, device=dev) for _ in range(2)]
-                mode += " + CUDA-graph replay of the upload (pinot_b200.CapturedBatchUpload)"
+    def e2e_loop(n_steps):
+        """Every step uploads its own inputs from pinned host memory and reads its loss back;
+        the upload of step k+1 overlaps the compute of step k (two-deep pipeline)."""
+        nxt = upload()
+        loss_host = None
+        for k in range(n_steps):
+            gs, yy, ev = nxt
+            torch.cuda.current_stream().wait_event(ev)
+            if captured is not None:
+                captured.load(gs, yy)                # device copy into the captured inputs
+                loss_dev = captured()                # one graph launch
+            else:
+                loss_dev = step(gs, yy)              # asynchronous launches
+            if k + 1 < n_steps:
+                nxt = upload()                       # next step's H2D + index build meanwhile
+            loss_host = float(loss_dev.item())       # device -> host read of the loss
+            net.output_regressor.verify()
+            step_marks.append(time.perf_counter())
+        return loss_host
 
-                def upload():                              # noqa: F811 - same contract as the eager upload above
-                    u = uploads[n_up[0] % 2]
-                    n_up[0] += 1
-                    return u.replay()
-            except Exception as exc:  # noqa: BLE001
-                sys.stderr.write("bench.py: CUDA-graph capture of the upload failed (%s); eager upload\n" % exc)
-                uploads = None
+    import gc
+    e2e_loop(5)
+    gc.collect()
+    gc.disable()                                     # no collector pauses inside the timed loop
+    ctx.barrier()
+    t0 = time.perf_counter()
+    e2e_loop(steps)
+    ctx.barrier()
+    e2e_s = ctx.max_over_ranks(time.perf_counter() - t0)
+    gc.enable()
+    e2e = {"value": n_mol * world * steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
+           "d2h_bytes_per_step": 4, "ms_per_step": 1e3 * e2e_s / steps, "mode": mode,
+           "includes": "per step: H2D of edges/features/targets from pinned memory + CSR build (copy stream, "
+                       "overlapping the previous step), train step, loss.item()"}
+    marks = step_marks[-steps:]
+    e2e["per_step_ms"] = [round(1e3 * (b - a), 3) for a, b in zip([t0] + marks[:-1], marks)]
+    if captured is not None:
+        # the same replay with resident inputs, device-timed like `value` (L2 flushed between steps)
+        ts = []
+        for _ in range(steps):
+            flush_buf.zero_()
+            s_ev, e_ev = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s_ev.record()
+            captured()
+            e_ev.record()
+            torch.cuda.synchronize()
+            ts.append(s_ev.elapsed_time(e_ev))
+        e2e["captured_step_device_ms"] = ctx.max_over_ranks(sum(ts) / len(ts))
+        captured.release()     # the graph holds the NCCL all-reduce: it must go before the process group
+    if uploads is not None:
+        for u in uploads:
+            u.release()
+    res["e2e"] = e2e
+    return res
 
-        def e2e_loop(n_steps):
-            """Every step uploads its own inputs from pinned host memory and reads its loss back;
-            the upload of step k+1 overlaps the compute of step k (two-deep pipeline)."""
-            nxt = upload()
-            for k in range(n_steps):
-                gs, yy, ev = nxt
-                torch.cuda.current_stream().wait_event(ev)
-                ta = time.perf_counter()
-                if captured is not None:
-                    captured.load(gs, yy)                # device copy into the captured inputs
-                    loss_dev = captured()                # one graph launch
-                else:
-                    loss_dev = step(gs, yy)              # asynchronous launches
-                tb = time.perf_counter()
-                if k + 1 < n_steps:
-                    nxt = upload()                       # next step's H2D + index build meanwhile
-                tc = time.perf_counter()
-                loss_host = float(loss_dev.item())       # device -> host read of the loss
-                net.output_regressor.verify()
-                step_marks.append(time.perf_counter())
-                if os.environ.get("PINOT_B200_BENCH_DEBUG"):
-                    sys.stderr.write("e2e step %d: launch %.2f ms, upload %.2f ms, wait %.2f ms\n" % (
-                        k, 1e3 * (tb - ta), 1e3 * (tc - tb), 1e3 * (step_marks[-1] - tc)))
-            return loss_host
 
-        import gc
-        e2e_loop(5)
-        gc.collect()
-        gc.disable()                                     # no collector pauses inside the timed loop
-        barrier()
-        t0 = time.perf_counter()
-        e2e_loop(args.steps)
-        barrier()
-        e2e_s = pbd.max_over_ranks(time.perf_counter() - t0, dev)
-        gc.enable()
-        e2e = {"value": n_mol * world * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
-               "d2h_bytes_per_step": 4, "ms_per_step": 1e3 * e2e_s / args.steps, "mode": mode,
-               "includes": "per step: H2D of edges/features/targets from pinned memory + CSR build (copy stream, overlapping the previous step), train step, loss.item()"}
-        marks = step_marks[-args.steps:]
-        e2e["per_step_ms"] = [round(1e3 * (b - a), 3) for a, b in zip([t0] + marks[:-1], marks)]
-        if captured is not None:
-            # the same replay with resident inputs, device-timed like `value` (L2 flushed between steps)
-            ts = []
-            for _ in range(args.steps):
-                flush_buf.zero_()
-                s_ev, e_ev = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                s_ev.record()
-                captured()
-                e_ev.record()
-                torch.cuda.synchronize()
-                ts.append(s_ev.elapsed_time(e_ev))
-            e2e["captured_step_device_ms"] = pbd.max_over_ranks(sum(ts) / len(ts), dev)
-            captured.release()     # the graph holds the NCCL all-reduce: it must go before the process group
-            captured = None
-        if uploads is not None:
-            for u in uploads:
-                u.release()
+def rooflines(res):
+    """One roofline entry per timed C-ABI entry point (algorithmic work of SURVEY.md 8d / DESIGN.md section 4
+    over the CUDA-event duration of the call inside the timed steps); the first one returned is the
+    entry point with the largest share of the step."""
+    from pinot_b200 import ops
+    hbm_peak, tf_peak, peak_src = measured_peaks()
+    tf32 = profile_json("tf32_peaks.json")
+    n, nn_, ne_ = res["n_mol"], res["nodes"], res["edges"]
+    sweep_flop = float(n) ** 3 / 3.0 + float(n) ** 2 + (float(n) ** 3 / 3.0 if getattr(ops, "LOSS_SWEEP_IDENTITY_ROWS", True) else 0.0)
+    table = {
+        "potrf_ext": ("tensor", sweep_flop,
+                      "Cholesky sweep of the stacked matrix [K + (eps + sigma^2) I ; y^T%s] (pinot_b200_potrf_ext): "
+                      "factor N^3/3 + extension rows" % (" ; I" if getattr(ops, "LOSS_SWEEP_IDENTITY_ROWS", True) else ""),
+                      "tgemm_kernel"),
+        "gp_nll_grad": ("tensor", float(n) ** 3 / 3.0,
+                        "closed-form marginal-likelihood gradient 0.5 L^-T diag(L) L^-1 - 0.5 alpha alpha^T "
+                        "(pinot_b200_gp_nll_grad: hi/lo split pass + TMA-fed tcgen05 3xTF32 GEMM)", "tgemm_tma_kernel"),
+        "trtri_lower": ("tensor", float(n) ** 3 / 3.0, "triangular inverse L^-1 (pinot_b200_trtri_lower)", "trtri"),
+        "gram_fwd": ("hbm", 2.0 * n * n + 8.0 * HIDDEN * n, "Gram matrix, lower tiles only (pinot_b200_gram_fwd)", "gram_fwd"),
+        "gram_bwd": ("hbm", 4.0 * n * n + 12.0 * HIDDEN * n, "Gram backward: reads dK once (pinot_b200_gram_bwd)", "gram_bwd"),
+        "mp_csr_aggregate_fwd": ("hbm", 8.0 * HIDDEN * nn_ + 4.0 * ne_ + 4.0 * (nn_ + 1) + 8.0 * nn_,
+                                 "message passing forward (mp_aggregate_kernel)", "mp_aggregate"),
+        "mp_csr_aggregate_bwd": ("hbm", 8.0 * HIDDEN * nn_ + 4.0 * ne_ + 4.0 * (nn_ + 1) + 8.0 * nn_,
+                                 "message passing backward (mp_aggregate_kernel on the transposed CSR)", "mp_aggregate"),
+        "node_update_fwd": ("hbm", 8.0 * HIDDEN * nn_ + 4.0 * HIDDEN * HIDDEN,
+                            "node update tanh(XW + b), average of the four layers (node_gemm_kernel)", "node_gemm_c2"),
+        "node_update_bwd": ("hbm", 16.0 * HIDDEN * nn_ + 8.0 * HIDDEN * HIDDEN,
+                            "node update backward: dZ, dX = dZ W^T, dW = X^T dZ, db (reads dY, Y, X; writes dX)", "node_bwd"),
+    }
+    out = []
+    for name, sh in sorted(res["shares"].items(), key=lambda kv: -kv[1]["share_of_step"]):
+        if name not in table:
+            continue
+        bound, work, what, ncu_key = table[name]
+        per_s = work / (sh["ms_per_call"] * 1e-3)
+        if bound == "tensor":
+            ach, peak, unit = per_s / 1e12, tf_peak, "TFLOP/s"
+        else:
+            ach, peak, unit = per_s / 1e9, hbm_peak, "GB/s"
+        e = {"kernel": what, "entry_point": "pinot_b200_" + name, "bound": bound, "achieved": ach, "peak": peak,
+             "unit": unit, "frac": ach / peak, "peak_source": peak_src + (", bf16 sustained" if bound == "tensor" else ""),
+             "share_of_step": sh["share_of_step"], "ms_per_call": sh["ms_per_call"], "calls_per_step": sh["calls_per_step"],
+             "algorithmic_work_per_call": work, "traffic": ncu_traffic(ncu_key) if n == N_MOL else None}
+        if bound == "tensor":
+            e["note"] = ("fp32-parity path: every product is 3 TF32 MMAs (hi.hi + hi.lo + lo.hi), so the tensor pipe "
+                         "executes 3x the algorithmic flops at the TF32 rate")
+            if tf32.get("tf32_dense_tflops_sustained"):
+                e["frac_of_tf32_peak"] = ach / tf32["tf32_dense_tflops_sustained"]
+                e["frac_of_3xtf32_ceiling"] = 3.0 * ach / tf32["tf32_dense_tflops_sustained"]
+                e["tf32_peak_source"] = tf32.get("_file")
+        elif n <= N_MOL:
+            e["note"] = "activations / matrices of this workload are L2-resident inside the step; HBM-sized runs: benchmarks/kernel_bench.py"
+        out.append(e)
+    return out
 
-    # ---- second headline number of BASELINE.json: exact-GP fit at N = 16 384 (embeddings given):
-    #      Gram + sweep (factor, L^-1 y, L^-T) + NLL + closed-form gradients, one GPU ----
-    fit16k = None
-    if rank == 0 and not args.no_fit16k:
-        from pinot_b200 import ops
-        n16, d16 = 16384, HIDDEN
-        gen = torch.Generator(device="cpu").manual_seed(0)
-        x16 = (0.1 * torch.randn(n16, d16, generator=gen)).to(dev).requires_grad_(True)
-        y16 = torch.randn(n16, 1, generator=gen).to(dev)
-        sc16 = torch.zeros(d16, device=dev, requires_grad=True)
-        var16 = torch.zeros((), device=dev, requires_grad=True)
-        ls16 = torch.tensor(-3.0, device=dev, requires_grad=True)
+
+def fit16k(ctx):
+    """Second headline number of BASELINE.json: exact-GP fit at N = 16 384 (embeddings given):
+    Gram + sweep + NLL + closed-form gradients, one GPU."""
+    from pinot_b200 import ops
+    dev = ctx.dev
+    n16, d16 = 16384, HIDDEN
+    gen = torch.Generator(device="cpu").manual_seed(0)
+    x16 = (0.1 * torch.randn(n16, d16, generator=gen)).to(dev).requires_grad_(True)
+    y16 = torch.randn(n16, 1, generator=gen).to(dev)
+    sc16 = torch.zeros(d16, device=dev, requires_grad=True)
+    var16 = torch.zeros((), device=dev, requires_grad=True)
+    ls16 = torch.tensor(-3.0, device=dev, requires_grad=True)
+
+    def fit():
+        for t in (x16, sc16, var16, ls16):
+            t.grad = None
+        ops.exact_gp_loss(x16, y16, sc16, var16, ls16).sum().backward()
+
+    fit()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(3):
+        ctx.flush_buf.zero_()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        fit()
+        e.record()
+        torch.cuda.synchronize()
+        ts.append(s.elapsed_time(e))
+    del x16, y16
+    torch.cuda.empty_cache()
+    return {"value": sorted(ts)[1], "unit": "ms", "n": n16, "d": d16,
+            "what": "Gram + Cholesky sweep + NLL + gradients w.r.t. embeddings and hyper-parameters, fp32 "
+                    "(3xTF32 tensor-core updates), 1 GPU, median of 3"}
+
+
+def sharded_fit(ctx, sizes=(16384, 65536), block=512, reps=3):
+    """the same fit with Gram + Cholesky sweep sharded over all ranks (strong scaling:
+    the problem is fixed, the ranks split it).  At world size 1 this is the blocked path on one GPU."""
+    from pinot_b200 import sharded_gp
+    dev, rank, world = ctx.dev, ctx.rank, ctx.world
+    out = []
+    for n in sizes:
+        gen = torch.Generator().manual_seed(0)
+        x = 0.1 * torch.randn(n, HIDDEN, generator=gen)
+        y = torch.randn(n, 1, generator=gen)
+        r0, r1 = n * rank // world, n * (rank + 1) // world
+        xl = x[r0:r1].to(dev).requires_grad_(True)
+        yl = y[r0:r1].to(dev)
+        sc = torch.zeros(HIDDEN, device=dev, requires_grad=True)
+        var = torch.zeros((), device=dev, requires_grad=True)
+        ls = torch.tensor(-3.0, device=dev, requires_grad=True)
 
         def fit():
-            for t in (x16, sc16, var16, ls16):
+            for t in (xl, sc, var, ls):
                 t.grad = None
-            ops.exact_gp_loss(x16, y16, sc16, var16, ls16).sum().backward()
+            sharded_gp.sharded_exact_gp_loss(xl, yl, sc, var, ls, block=block, check=False).sum().backward()
 
         fit()
-        torch.cuda.synchronize()
         ts = []
-        for _ in range(3):
-            flush_buf.zero_()
+        for _ in range(reps):
+            ctx.barrier()
             s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             s.record()
             fit()
             e.record()
             torch.cuda.synchronize()
             ts.append(s.elapsed_time(e))
-        fit16k = {"value": sorted(ts)[1], "unit": "ms", "n": n16, "d": d16,
-                  "what": "Gram + Cholesky sweep with L^-1 y and L^-T + NLL + gradients w.r.t. embeddings and "
-                          "hyper-parameters, fp32 (3xTF32 tensor-core updates), 1 GPU"}
-        del x16, y16
+        ms = ctx.max_over_ranks(sorted(ts)[len(ts) // 2])
+        out.append({"n": n, "d": HIDDEN, "n_gpus": world, "block": block, "fit_ms": ms, "scaling": "strong",
+                    "info": int(sharded_gp._ShardedExactGPLoss.last_info.item())})
+        del xl, yl
+        torch.cuda.empty_cache()
+    return out
+
+
+def bo_round(ctx, pool_chunk, n_train=4096, q=96, rounds=3):
+    """SURVEY.md 8(e-3) / configs[4]: one Thompson-sampling acquisition round over the 1 M-molecule pool
+    (8 chunks of ``pool_chunk`` molecules, seeds 100..107: the SAME pool at every world size, strong
+    scaling), block-partitioned over the ranks; training set of ``n_train`` molecules replicated."""
+    import pinot_b200 as pb
+    from pinot_b200 import active, distributed as pbd, synthetic
+    from pinot_b200 import graph as pgraph
+    dev, rank, world = ctx.dev, ctx.rank, ctx.world
+    if POOL_CHUNKS % world != 0:
+        return {"skipped": "world size %d does not divide the %d pool chunks" % (world, POOL_CHUNKS)}
+    torch.manual_seed(0)
+    net = pb.Net(pb.representation.Sequential(pb.representation.dgl_legacy.gn(), CONFIG),
+                 output_regressor_class=pb.regressors.ExactGaussianProcessRegressor).to(dev)
+    with torch.no_grad():
+        net.output_regressor.kernel.scale.fill_(KERNEL_SCALE)
+    pbd.broadcast_parameters(net)
+    g_tr, y_tr = synthetic.make_batch(n_train, seed=11, device=dev)
+    per = POOL_CHUNKS // world
+    t0 = time.perf_counter()
+    parts = [synthetic.make_batch(pool_chunk, seed=100 + c)[0] for c in range(rank * per, (rank + 1) * per)]
+    pool = (parts[0] if per == 1 else pgraph.batch(parts)).to(dev)
+    del parts
+    gen_s = time.perf_counter() - t0
+    pool.csr()
+    n_local = pool.batch_size
+    net.g_last, net.y_last = g_tr, y_tr          # what Net.loss would have cached (pinot/net.py:191-193)
+    offset = rank * n_local
+
+    def one_round():
+        picks = active.thompson_sampling_sharded(net, pool, offset, q=q)
+        mine = [int(p) - offset for p in picks.tolist() if offset <= int(p) < offset + n_local]
+        return pool.select(sorted(set(mine))) if mine else None
+
+    one_round()
+    ctx.barrier()
+    evs = []
+    for _ in range(rounds):
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        one_round()
+        e.record()
+        evs.append((s, e))
+    torch.cuda.synchronize()
+    ms = ctx.max_over_ranks(sum(s.elapsed_time(e) for s, e in evs) / rounds)
+    total = n_local * world
+    del pool
+    torch.cuda.empty_cache()
+    return {"workload": "C5: Thompson-sampling acquisition round over a %d-molecule pool (%d per GPU), training set "
+                        "%d, q = %d: embed + factor the training set, embed and score the pool (marginal posterior), "
+                        "q draws, global arg-max (one all-gather), device-side re-batching of the winners"
+                        % (total, n_local, n_train, q),
+            "n_gpus": world, "ms_per_round": ms, "pool_molecules_per_s": total / (ms * 1e-3), "scaling": "strong",
+            "pool_generation_s_host": gen_s}
+
+
+def b200_main(args):
+    ctx = Ctx()
+    rank, world = ctx.rank, ctx.world
+    n_mol = args.molecules
+    main = measure_train_step(ctx, n_mol, args.steps, args.warmup, want_e2e=not args.no_e2e, sample_clocks=True)
+    rl = rooflines(main)
+
+    # ---- configs[0] / C1: the ESOL-shaped workload north_star's ">= 50x" target is stated on ----
+    c1 = None
+    if world == 1 and not args.no_c1 and n_mol != N_MOL_C1:
+        r1 = measure_train_step(ctx, N_MOL_C1, args.steps, args.warmup, want_e2e=not args.no_e2e, sample_clocks=False)
+        c1 = {"config": workload_config(N_MOL_C1, 1, "C1 (ESOL shape)"), "value": r1["value"], "unit": UNIT,
+              "ms_per_step": r1["ms_per_step"], "e2e": r1["e2e"], "gpu_launches": r1["launches"],
+              "kernel_shares": r1["shares"], "final_loss": r1["final_loss"]}
+        if not args.no_cpu_baseline:
+            c = cpu_arm(N_MOL_C1, steps=5, warmup=2, budget_s=30.0)
+            c1["cpu_baseline"] = {"value": c["value"], "unit": UNIT, "cores": c["cores"], "kind": "port",
+                                  "sample": c["sample"], "ms_per_step": c["ms_per_step"]}
+            c1["speedup_vs_cpu_port"] = {"device": r1["value"] / c["value"],
+                                         "e2e": (r1["e2e"]["value"] / c["value"]) if r1["e2e"] else None}
+
+    fit = None
+    if rank == 0 and not args.no_fit16k:
+        fit = fit16k(ctx)
+        if world == 1 and not args.no_cpu_baseline:
+            fit["cpu_baseline"] = cpu_fit_baseline()
+            fit["speedup_vs_cpu_port"] = fit["cpu_baseline"]["value"] / fit["value"]
+    ctx.barrier()
+
+    sharded, bo = None, None
+    if not args.no_extras:
+        sharded = sharded_fit(ctx)
+        if fit is not None and sharded:
+            for s in sharded:
+                if s["n"] == fit["n"]:
+                    s["fused_single_gpu_ms"] = fit["value"]
+        bo = bo_round(ctx, args.pool_chunk)
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        v, ms, cores, sample = cpu_arm(n_mol, steps=2, warmup=1, budget_s=40.0)
-        cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
-                        "ms_per_step": ms}
+        c = cpu_arm(n_mol, steps=3, warmup=1, budget_s=90.0)
+        cpu_baseline = {"value": c["value"], "unit": UNIT, "cores": c["cores"], "kind": "port", "sample": c["sample"],
+                        "ms_per_step": c["ms_per_step"], "molecules": c["molecules"]}
 
     if rank == 0:
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(n_mol, world),
-            "roofline": roofline, "roofline_other_kernels": extra, "kernel_shares": shares,
-            "exact_gp_fit_n16k": fit16k, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
-            "final_loss": final_loss,
+            "metric": METRIC, "value": main["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": main["ms_per_step"], "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(n_mol, world, "C2" if n_mol == N_MOL else "custom"),
+            "roofline": rl[0] if rl else None, "roofline_other_kernels": rl[1:], "kernel_shares": main["shares"],
+            "c1_esol_shape": c1, "exact_gp_fit_n16k": fit, "sharded_gp_fit": sharded, "bo_round": bo,
+            "cpu_baseline": cpu_baseline, "e2e": main["e2e"], "gpu_launches": main["launches"],
+            "clocks": main["clocks"], "final_loss": main["final_loss"],
         }
         print(json.dumps(line))
     if world > 1:

@@ -43,7 +43,10 @@ PINOT_B200_API int64_t pinot_b200_launch_count(void);
 /* ---------------------------------------------------------------------------------------------
  * Kernel (1): message passing.
  * out[i,:] = dst_scale[i] * sum_{e in [indptr[i],indptr[i+1])} src_scale[indices[e]] * x[indices[e],:]
- * (either scale pointer may be NULL = 1).  CSR is sorted by destination node.
+ * (either scale pointer may be NULL = 1).  CSR is sorted by destination node.  Source and destination
+ * nodes are ONE node set: x and out both have n_dst rows and every entry of indices lies in [0, n_dst)
+ * (molecular graphs; a bipartite / block graph with more source rows than n_dst is not supported -- the
+ * kernel chooses 32-bit row offsets from n_dst * feat).
  * Replaces dgl.nn.pytorch.conv.GraphConv(norm="both") / SAGEConv("mean")'s
  * update_all(copy_src, sum|mean) reached from pinot/representation/dgl_legacy.py:40-50
  * (GraphConv: src_scale = out_deg^-1/2, dst_scale = in_deg^-1/2, degrees clamped to >= 1;
@@ -183,7 +186,8 @@ PINOT_B200_API int64_t pinot_b200_potrf_tma_scratch_bytes(int64_t n, int64_t n_e
 PINOT_B200_API int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, int ext_identity,
                          float* diag_out, void* workspace, int64_t workspace_bytes, int* info,
                          cudaStream_t stream);
-/* The same sweep as pinot_b200_potrf_ext for callers that cannot hand over scratch memory.
+/* The factorisation of pinot_b200_potrf_ext (same arguments, same outputs up to rounding) for callers
+ * that cannot hand over scratch memory.
  * (No counterpart in the reference: pinot lets torch allocate whatever cuSOLVER asks for.)
  *
  * Who needs it: code that receives device buffers from a host framework but has no way to obtain
@@ -194,10 +198,20 @@ PINOT_B200_API int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t
  * freed, here or in any routine it calls.  Inputs and outputs (e, diag_out, info) are still the
  * caller's.
  *
+ * It is NOT the schedule of pinot_b200_potrf_ext: it runs the plain right-looking sweep, two launches
+ * per 64-column panel (one kernel factors the diagonal block and solves the panel on CUDA cores, one
+ * tensor-core GEMM applies the trailing update), without the look-ahead factor, the tensor-core panel
+ * solve or the two-level blocking that need flags and inverse blocks in a workspace.  It is therefore
+ * slower than pinot_b200_potrf_ext (DESIGN.md section 4 has the measured pair).
+ *
  * Limits and rules:
  *   - n <= PINOT_B200_POTRF_NOALLOC_MAX_N; larger n returns code 3 with a message naming the limit;
+ *     n + n_ext_dense (+ n with ext_identity) must stay below 2^30 rows;
+ *   - the GPU that holds `e` must be the CURRENT device of the calling thread (the built-in array is
+ *     per device; a mismatch returns code 1 instead of touching another GPU's memory);
  *   - the first call on each device looks up the array's device address (once, cached); make that
- *     first call before starting any stream capture on that device;
+ *     first call before starting any stream capture on that device.  The cached address does not
+ *     survive cudaDeviceReset(): do not reset a device between calls;
  *   - every call on a device uses the same array: two calls that may overlap on the GPU (different
  *     streams, or different host threads) race with each other -- serialise them.  Back-to-back
  *     calls on one stream are fine; nothing needs clearing in between because each call overwrites

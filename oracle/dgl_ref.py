@@ -196,6 +196,38 @@ def sage_conv_mean(graph, feat, w_self, b_self, w_neigh, b_neigh):
     return rst
 
 
+def gin_conv(graph, feat, eps=0.0, aggregator_type="sum"):
+    """Functional GINConv body before ``apply_func`` (DGL's documented definition):
+    ``(1 + eps) * x_i + aggregate_{j->i} x_j`` with aggregate = sum or mean."""
+    s = _sum_over_in_edges(graph, feat)
+    if aggregator_type == "mean":
+        deg = graph.in_degrees().to(feat.dtype)
+        s = torch.where(deg.reshape(-1, 1) > 0, s / deg.clamp(min=1).reshape(-1, 1), torch.zeros_like(s))
+    return (1 + eps) * feat + s
+
+
+def sym_in_powers(graph, feat, k):
+    """[x, S x, ..., S^k x], S = D^-1/2 A D^-1/2 with D = in-degrees clamped to >= 1 on BOTH sides
+    (DGL's SGConv / TAGConv normalisation)."""
+    norm = torch.pow(graph.in_degrees().to(feat.dtype).clamp(min=1), -0.5).reshape(-1, 1)
+    out = [feat]
+    for _ in range(int(k)):
+        out.append(_sum_over_in_edges(graph, out[-1] * norm) * norm)
+    return out
+
+
+def sg_conv(graph, feat, w, b, k=1):
+    """Functional SGConv: ``fc(S^k x)``, ``w`` in torch.nn.Linear layout (out, in)."""
+    h = sym_in_powers(graph, feat, k)[-1] @ w.t()
+    return h + b if b is not None else h
+
+
+def tag_conv(graph, feat, w, b, k=2):
+    """Functional TAGConv: ``lin(cat([x, S x, ..., S^k x], dim=-1))``, ``w`` of shape (out, in * (k + 1))."""
+    h = torch.cat(sym_in_powers(graph, feat, k), dim=-1) @ w.t()
+    return h + b if b is not None else h
+
+
 class GraphConv(torch.nn.Module):
     def __init__(self, in_feats, out_feats, norm="both", weight=True, bias=True, activation=None):
         super().__init__()
@@ -236,6 +268,45 @@ class SAGEConv(torch.nn.Module):
         return rst
 
 
+class GINConv(torch.nn.Module):
+    def __init__(self, apply_func=None, aggregator_type="sum", init_eps=0, learn_eps=False):
+        super().__init__()
+        self.apply_func, self._aggregator_type = apply_func, aggregator_type
+        if learn_eps:
+            self.eps = torch.nn.Parameter(torch.FloatTensor([init_eps]))
+        else:
+            self.register_buffer("eps", torch.FloatTensor([init_eps]))
+
+    def forward(self, graph, feat):
+        rst = gin_conv(graph, feat, self.eps, self._aggregator_type)
+        return self.apply_func(rst) if self.apply_func is not None else rst
+
+
+class SGConv(torch.nn.Module):
+    def __init__(self, in_feats, out_feats, k=1, cached=False, bias=True, norm=None):
+        super().__init__()
+        self.fc = torch.nn.Linear(in_feats, out_feats, bias=bias)
+        self._k = k
+        torch.nn.init.xavier_uniform_(self.fc.weight)
+        if self.fc.bias is not None:
+            torch.nn.init.zeros_(self.fc.bias)
+
+    def forward(self, graph, feat):
+        return sg_conv(graph, feat, self.fc.weight, self.fc.bias, self._k)
+
+
+class TAGConv(torch.nn.Module):
+    def __init__(self, in_feats, out_feats, k=2, bias=True, activation=None):
+        super().__init__()
+        self.lin = torch.nn.Linear(in_feats * (k + 1), out_feats, bias=bias)
+        self._k, self._activation = k, activation
+        torch.nn.init.xavier_uniform_(self.lin.weight, gain=torch.nn.init.calculate_gain("relu"))
+
+    def forward(self, graph, feat):
+        rst = tag_conv(graph, feat, self.lin.weight, self.lin.bias, self._k)
+        return self._activation(rst) if self._activation is not None else rst
+
+
 def as_module(name="dgl"):
     """A module object exposing this file under DGL's names (dgl, dgl.nn.pytorch.conv)."""
     import importlib.machinery
@@ -253,6 +324,7 @@ def as_module(name="dgl"):
     pt = _mod(name + ".nn.pytorch")
     conv = _mod(name + ".nn.pytorch.conv")
     conv.GraphConv, conv.SAGEConv = GraphConv, SAGEConv
+    conv.GINConv, conv.SGConv, conv.TAGConv = GINConv, SGConv, TAGConv
     pt.conv = conv
     pt.GraphConv, pt.SAGEConv = GraphConv, SAGEConv
     nn.pytorch = pt

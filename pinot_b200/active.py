@@ -40,11 +40,11 @@ def slice_fn_tuple(x, idxs):
     return slice_fn_graph(gs, idxs), slice_fn_tensor(ys, idxs)
 
 
-def _independent(net, gs):
+def _independent(net, gs, row_offset=0):
     """``pinot.metrics._independent(net.condition(gs))`` -- through the marginal path when the net
-    offers one."""
+    offers one.  ``row_offset``: pool index of the first molecule of ``gs`` when it is one shard of the pool."""
     if hasattr(net, "condition_marginal") and getattr(net, "has_exact_gp", False):
-        return net.condition_marginal(gs)
+        return net.condition_marginal(gs, row_offset=row_offset)
     d = net.condition(gs)
     return torch.distributions.normal.Normal(loc=d.mean.flatten(), scale=d.variance.pow(0.5).flatten())
 
@@ -70,7 +70,7 @@ def thompson_sampling_sharded(net, gs_local, global_offset, q=1, generator=None)
     arg-max of each draw is found with one all-gather of (value, index) pairs.  ``global_offset`` is
     the pool index of this rank's first molecule.  Returns ``q`` global indices (duplicates possible),
     identical on every rank."""
-    distribution = _independent(net, gs_local)
+    distribution = _independent(net, gs_local, row_offset=int(global_offset))
     n_local = distribution.loc.numel()
     eps = torch.randn((q, n_local), device=distribution.loc.device, generator=generator)
     thetas = distribution.loc + distribution.scale * eps

@@ -42,21 +42,30 @@ class CapturedTrainStep:
                     setattr(obj, name, None)
         params = [p for p in net.parameters()]
         saved = [p.detach().clone() for p in params]
+        # optimizer state that exists BEFORE the first step (e.g. Adagrad's initial accumulator) is restored
+        # value for value after the warm-up; state that the first step creates lazily starts from zeros
+        # (Adam's moments and step counter, momentum buffers), which is what zeroing restores
+        state0 = {p: {k: v.detach().clone() for k, v in st.items() if torch.is_tensor(v)}
+                  for p, st in optimizer.state.items()}
         cur = torch.cuda.current_stream(dev)
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(cur)
         with torch.cuda.stream(side):
             for _ in range(max(int(warmup), 1)):
                 self._eager()
-            # undo the warm-up: parameters back, optimizer state zeroed in place (it must exist, at
-            # fixed addresses, before the capture)
+            # undo the warm-up in place: parameters back, optimizer state back to its initial values (it
+            # must exist, at fixed addresses, before the capture)
             with torch.no_grad():
                 for p, s in zip(params, saved):
                     p.copy_(s)
-                for st in optimizer.state.values():
-                    for v in st.values():
+                for p, st in optimizer.state.items():
+                    for k, v in st.items():
                         if torch.is_tensor(v):
-                            v.zero_()
+                            before = state0.get(p, {}).get(k)
+                            if before is not None:
+                                v.copy_(before)
+                            else:
+                                v.zero_()
         cur.wait_stream(side)
         torch.cuda.synchronize(dev)
         optimizer.zero_grad(set_to_none=True)

@@ -348,6 +348,8 @@ int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, i
                          float* diag_out, void* workspace, int64_t workspace_bytes, int* info,
                          cudaStream_t stream) {
     PB_REQUIRE(n >= 0 && n < (1ll << 30) && n_ext_dense >= 0 && ld >= n, "potrf_ext: invalid sizes");
+    PB_REQUIRE(n_ext_dense < (1ll << 30) && 2 * n + n_ext_dense < (1ll << 30),
+               "potrf_ext: %lld rows exceed the 2^30 row limit", (long long)(2 * n + n_ext_dense));
     PB_REQUIRE(info, "potrf_ext: info pointer is required");
     PB_CUDA(cudaMemsetAsync(info, 0, sizeof(int), stream));
     if (n == 0) return pb::PB_OK;
@@ -526,6 +528,8 @@ int noalloc_scratch_for_current_device(float** out) {
 int pinot_b200_potrf_ext_noalloc(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, int ext_identity,
                                  float* diag_out, int* info, cudaStream_t stream) {
     PB_REQUIRE(n >= 0 && n_ext_dense >= 0 && ld >= n, "potrf_ext_noalloc: invalid sizes");
+    PB_REQUIRE(n_ext_dense < (1ll << 30) && 2 * n + n_ext_dense < (1ll << 30),
+               "potrf_ext_noalloc: %lld rows exceed the 2^30 row limit", (long long)(2 * n + n_ext_dense));
     PB_REQUIRE(info, "potrf_ext_noalloc: info pointer is required");
     if (n > kNoAllocMaxN) {
         pb::set_error("potrf_ext_noalloc: n = %lld exceeds the built-in scratch limit of %lld rows; call "
@@ -536,6 +540,18 @@ int pinot_b200_potrf_ext_noalloc(float* e, int64_t ld, int64_t n, int64_t n_ext_
     float* wdiag = nullptr;
     int rc = noalloc_scratch_for_current_device(&wdiag);
     if (rc) return rc;
+    if (e) {
+        // the built-in array belongs to the current device: refuse a matrix that lives on another GPU
+        cudaPointerAttributes attr;
+        int cur = -1;
+        if (cudaPointerGetAttributes(&attr, e) == cudaSuccess && cudaGetDevice(&cur) == cudaSuccess &&
+            attr.type == cudaMemoryTypeDevice && attr.device != cur) {
+            pb::set_error("potrf_ext_noalloc: the matrix lives on device %d but device %d is current; make the "
+                          "matrix's device current before the call", attr.device, cur);
+            return pb::PB_ERR_ARG;
+        }
+        (void)cudaGetLastError();
+    }
     PB_CUDA(cudaMemsetAsync(info, 0, sizeof(int), stream));
     if (n == 0) return pb::PB_OK;
     PB_REQUIRE(e, "potrf_ext_noalloc: null pointer");

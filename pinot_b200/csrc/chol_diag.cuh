@@ -120,11 +120,19 @@ __device__ __forceinline__ void publish_flag(int* flag) {
     if (threadIdx.x == 0) atomicExch(flag, 1);   // ... before the flag is
 }
 __device__ __forceinline__ void wait_flag(const int* flag) {
+    // The flag is published by CTA (0,0) of the SAME grid.  Blocks are dispatched in ascending index order,
+    // so that CTA is resident (or finished) whenever a waiter runs; CUDA's forward-progress model does not
+    // promise it, hence the bounded spin: after ~2 s without the flag the kernel traps (a launch error the
+    // host sees) instead of hanging the GPU.
     if (threadIdx.x == 0) {
         int v;
+        unsigned spins = 0;
         do {
             asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
-            if (v == 0) __nanosleep(64);
+            if (v == 0) {
+                __nanosleep(64);
+                if (++spins > (1u << 25)) __trap();
+            }
         } while (v == 0);
     }
     __syncthreads();

@@ -122,6 +122,8 @@ class GraphCSR:
     def scales(self, norm):
         if norm == "both":
             return self.out_norm, self.in_norm
+        if norm == "sym_in":     # SGConv / TAGConv: the in-degree normalises both sides
+            return self.in_norm, self.in_norm
         if norm == "mean":
             return None, self.inv_in_deg
         if norm == "none":

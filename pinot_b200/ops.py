@@ -13,6 +13,9 @@ from ._lib import call, ptr
 
 EPSILON = 1e-5  # GaussianProcessRegressor.epsilon, pinot/regressors/gaussian_process_regressor.py:20
 KIND = {"rbf": 0, "matern52": 1}
+#: the exact-GP loss obtains L^-T from N identity extension rows riding through the sweep (bench.py counts
+#: their N^3/3 flops as algorithmic work of the potrf_ext call)
+LOSS_SWEEP_IDENTITY_ROWS = True
 
 
 def _f32c(t):
@@ -389,8 +392,10 @@ class ExactGPPosterior:
         self._e = e
 
     @torch.no_grad()
-    def mean_var(self, x_te, chunk=32768):
-        """Predictive mean and marginal variance, (n_te,) each, computed ``chunk`` test points at a time."""
+    def mean_var(self, x_te, chunk=32768, row_offset=0):
+        """Predictive mean and marginal variance, (n_te,) each, computed ``chunk`` test points at a time.
+        ``row_offset``: index of ``x_te[0]`` within the full test set when the caller scores it in pieces
+        (the rectangular ``_perturb`` sits on the GLOBAL main diagonal of K_te,tr)."""
         x_te = _f32c(x_te.detach())
         nte, n, dev = x_te.shape[0], self.n, x_te.device
         mean = torch.empty((nte,), device=dev, dtype=torch.float32)
@@ -398,8 +403,8 @@ class ExactGPPosterior:
         for r0 in range(0, nte, chunk):
             r1 = min(nte, r0 + chunk)
             g = gram_raw(self.kind, x_te[r0:r1], self.x_tr, self.scale, self.variance)
-            if r0 < n:   # _perturb of the rectangular K_te,tr: eps on its main diagonal (:95)
-                g.diagonal(offset=r0).add_(EPSILON)
+            if row_offset + r0 < n:   # _perturb of the rectangular K_te,tr: eps on its main diagonal (:95)
+                g.diagonal(offset=int(row_offset) + r0).add_(EPSILON)
             v = torch.empty((r1 - r0, n), device=dev, dtype=torch.float32)
             call("sgemm", 0, 0, r1 - r0, n, n, 1.0, ptr(g), n, ptr(self.linv_t), self.ld, 0.0, ptr(v), n)
             # variance from V (the mean V z of the same pass is discarded: the mean is taken as
@@ -411,13 +416,30 @@ class ExactGPPosterior:
         return mean, var
 
 
+    @torch.no_grad()
+    def mean_cov(self, x_te):
+        """Predictive mean (n_te,) and full covariance (n_te, n_te) from the cached factor:
+        ``V = K_te,tr L^-T``, ``cov = K_te,te - V V^T`` (gaussian_process_regressor.py:212-221; symmetric by
+        construction)."""
+        x_te = _f32c(x_te.detach())
+        nte, n, dev = x_te.shape[0], self.n, x_te.device
+        g = gram_raw(self.kind, x_te, self.x_tr, self.scale, self.variance, diag_add=EPSILON)
+        v = torch.empty((nte, n), device=dev, dtype=torch.float32)
+        call("sgemm", 0, 0, nte, n, n, 1.0, ptr(g), n, ptr(self.linv_t), self.ld, 0.0, ptr(v), n)
+        mean = torch.empty((nte,), device=dev, dtype=torch.float32)
+        call("gemv_rows", ptr(g), n, nte, n, 0, ptr(self.alpha), ptr(mean))
+        cov = gram_raw(self.kind, x_te, x_te, self.scale, self.variance, diag_add=EPSILON)
+        call("sgemm", 0, 1, nte, nte, n, -1.0, ptr(v), n, ptr(v), n, 1.0, ptr(cov), nte)
+        return mean, cov
+
+
 class _CholSolve(torch.autograd.Function):
     """(K, B) -> (L, X = L^-1 B) with K = L L^T; differentiable (generic Cholesky backward built
     from L^-T, which the same sweep provides).  Used by the variational GP
     (pinot/regressors/gaussian_process_regressor.py:373-390, :466-473)."""
 
     @staticmethod
-    def forward(ctx, k, b, check):
+    def forward(ctx, k, b, check, info_sink=None):
         k = _f32c(k)
         n = k.shape[0]
         dev = k.device
@@ -430,7 +452,9 @@ class _CholSolve(torch.autograd.Function):
             e[n:n + r, :n] = _f32c(b).t()
         if need_grad:
             e[n + r:, :n].diagonal().fill_(1.0)
-        potrf_ext_raw(e, n, n_ext_dense=r, ext_identity=need_grad, want_diag=False, check=check)
+        _, info = potrf_ext_raw(e, n, n_ext_dense=r, ext_identity=need_grad, want_diag=False, check=check)
+        if info_sink is not None:
+            info_sink.append(info)       # status stays on the device; the owner checks it when it synchronises
         l = e[:n, :n].clone()
         call("zero_upper", ptr(l), n, n)
         x = e[n:n + r, :n].t().contiguous() if r else None
@@ -457,18 +481,20 @@ class _CholSolve(torch.autograd.Function):
             s = matmul(matmul(w, p), w, False, True)        # L^-T P L^-1
             gk = 0.5 * (s + s.t())
         if not ctx.has_b:
-            return gk, None, None
-        return gk, (gb if ctx.needs_input_grad[1] else None), None
+            return gk, None, None, None
+        return gk, (gb if ctx.needs_input_grad[1] else None), None, None
 
 
-def cholesky(k, check=True):
-    """Lower Cholesky factor (zeros above the diagonal), differentiable."""
-    return _CholSolve.apply(k, None, check)
+def cholesky(k, check=True, info_sink=None):
+    """Lower Cholesky factor (zeros above the diagonal), differentiable.  With ``check=False`` the
+    LAPACK-style status stays on the device; ``info_sink`` (a list) receives that int tensor."""
+    return _CholSolve.apply(k, None, check, info_sink)
 
 
-def chol_solve(k, b, check=True):
-    """Returns ``(L, L^-1 b)`` for ``k = L L^T`` from one sweep, differentiable."""
-    return _CholSolve.apply(k, b, check)
+def chol_solve(k, b, check=True, info_sink=None):
+    """Returns ``(L, L^-1 b)`` for ``k = L L^T`` from one sweep, differentiable (``info_sink``: see
+    :func:`cholesky`)."""
+    return _CholSolve.apply(k, b, check, info_sink)
 
 
 def log_2pi():

@@ -116,6 +116,12 @@ class ExactGaussianProcessRegressor(GaussianProcessRegressor):
             full_cov=True, check=bool(self.check_positive_definite))
         return _mvn_from_cov(mean, cov, check=bool(self.check_positive_definite))
 
+    def condition_from_posterior(self, posterior, x_te):
+        """``condition`` from a training factorisation that is already available (``ops.ExactGPPosterior``,
+        kept by ``Net`` between calls): no second sweep over the training set."""
+        mean, cov = posterior.mean_cov(x_te)
+        return _mvn_from_cov(mean, cov, check=bool(self.check_positive_definite))
+
     def condition_marginal(self, x_te, x_tr=None, y_tr=None):
         """Predictive marginals ``Normal(mean, sqrt(var))`` without materialising the n_te x n_te
         covariance: what ``pinot.metrics._independent`` (pinot/metrics.py:13-27) extracts from
@@ -203,7 +209,17 @@ class VariationalGaussianProcessRegressor(GaussianProcessRegressor):
             torch.zeros(int(n_inducing_points * (n_inducing_points - 1) * 0.5)))
         self.n_inducing_points = n_inducing_points
         self.kl_loss_scaling = kl_loss_scaling
+        #: True / "deferred" / False, as for the exact head: "deferred" keeps the status of every
+        #: factorisation of the last ``loss`` / ``forward`` on the device until ``verify()`` reads it
         self.check_positive_definite = True
+        self._infos = []
+
+    def verify(self):
+        """Raise RuntimeError if a factorisation of the last ``loss`` / ``forward`` call met a non-positive
+        pivot (for ``check_positive_definite="deferred"``).  One device read per factorisation."""
+        if self.check_positive_definite:
+            for info in self._infos:
+                ops.check_info(info)
 
     def _kind(self):
         kind = getattr(self.kernel, "kind", None)
@@ -242,7 +258,8 @@ class VariationalGaussianProcessRegressor(GaussianProcessRegressor):
         k_tr_tr = self._k_tr_tr()
         k_tr_te = self._k_tr_te(x_te)
         rhs = torch.cat([self.y_tr_mu, self._y_tr_sigma(), k_tr_te], dim=1)
-        l, sol = ops.chol_solve(k_tr_tr, rhs, check=(self.check_positive_definite is True))
+        self._infos = []
+        l, sol = ops.chol_solve(k_tr_tr, rhs, check=(self.check_positive_definite is True), info_sink=self._infos)
         return l, sol[:, :1], sol[:, 1:1 + m], sol[:, 1 + m:]
 
     def forward(self, x_te):
@@ -276,7 +293,8 @@ class VariationalGaussianProcessRegressor(GaussianProcessRegressor):
         n = x_te.shape[0]
         m = self.n_inducing_points
         resid = (y_te.flatten() - predictive_mean.flatten()).reshape(n, 1)
-        l_cov, r = ops.chol_solve(predictive_cov, resid, check=(self.check_positive_definite is True))
+        l_cov, r = ops.chol_solve(predictive_cov, resid, check=(self.check_positive_definite is True),
+                                  info_sink=self._infos)
         half_log_det = torch.log(torch.diagonal(l_cov)).sum()
         log_prob = -0.5 * (r * r).sum() - half_log_det - 0.5 * n * math.log(2.0 * math.pi)
         nll = -log_prob  # `.mean()` of a scalar (:473)

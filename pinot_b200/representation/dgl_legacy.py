@@ -1,8 +1,16 @@
-"""``pinot.representation.dgl_legacy`` on pinot_b200 kernels (pinot/representation/dgl_legacy.py:15-72).
+"""Layer factory of ``pinot.representation.dgl_legacy`` on pinot_b200 kernels.
 
-``GN`` wraps a graph-convolution layer and exposes ``in_features`` / ``out_features`` so that
-``pinot.Net`` can discover the representation width (pinot/net.py:141-145); ``gn(model_name)`` is
-the layer factory handed to ``Sequential``.
+Contract (pinot/representation/dgl_legacy.py:15-72, pinned by tests/test_api.py):
+
+* ``gn(model_name="GraphConv", kwargs={})`` returns ``layer(in_features, out_features)``, the factory
+  that ``Sequential`` calls once per integer entry of its config;
+* the layer it builds is a ``GN``: attribute ``gn`` holds the convolution (so state_dict keys read
+  ``d{idx}.gn.weight``, ``d{idx}.gn.fc_self.weight`` ...), and ``in_features`` / ``out_features`` are
+  exposed for ``Net`` to read the representation width from (pinot/net.py:141-145);
+* with no ``kwargs`` a layer type takes the defaults of ``DEFAULT_MODEL_KWARGS`` (SAGEConv -> mean
+  aggregator, TAGConv -> k = 2);
+* ``gn("GINConv")`` is the one exception: it returns the bare GINConv with a ``Linear`` apply function
+  and the sum aggregator (:60-64).
 """
 import torch
 
@@ -15,31 +23,36 @@ DEFAULT_MODEL_KWARGS = {
 }
 
 
+def _conv_class(model_name):
+    cls = getattr(_conv, model_name, None) if model_name in _conv.__all__ else None
+    if cls is None:
+        raise NotImplementedError(
+            "pinot_b200 implements %s on its CSR kernels (SURVEY.md sections 8a, 8f-4); %r is not available"
+            % (", ".join(_conv.__all__), model_name))
+    return cls
+
+
 class GN(torch.nn.Module):
-    """Graph net layer; state_dict keys are ``gn.weight`` / ``gn.bias`` (GraphConv) or
-    ``gn.fc_self.*`` / ``gn.fc_neigh.*`` (SAGEConv), as in the reference."""
+    """One graph-convolution layer with the width attributes pinot expects."""
 
     def __init__(self, in_features, out_features, model_name="GraphConv", kwargs={}):
-        super(GN, self).__init__()
-        if kwargs == {}:
-            if model_name in DEFAULT_MODEL_KWARGS:
-                kwargs = DEFAULT_MODEL_KWARGS[model_name]
-        if not hasattr(_conv, model_name):
-            raise NotImplementedError(
-                "pinot_b200 implements GraphConv and SAGEConv (SURVEY.md section 8a); %r is not available"
-                % (model_name,))
-        self.gn = getattr(_conv, model_name)(in_features, out_features, **kwargs)
-        self.in_features = in_features
-        self.out_features = out_features
+        super().__init__()
+        options = dict(kwargs) if kwargs else dict(DEFAULT_MODEL_KWARGS.get(model_name, {}))
+        self.in_features, self.out_features = in_features, out_features
+        self.gn = _conv_class(model_name)(in_features, out_features, **options)
 
     def forward(self, g, x, _act=None):
-        if _act is not None:
-            return self.gn(g, x, _act=_act)
-        return self.gn(g, x)
+        # `_act` lets Sequential hand the following tanh to the layer's fused epilogue
+        return self.gn(g, x) if _act is None else self.gn(g, x, _act=_act)
 
 
 def gn(model_name="GraphConv", kwargs={}):
-    """Layer factory: ``gn()(in_features, out_features) -> GN``."""
-    return lambda in_features, out_features: GN(
-        in_features=in_features, out_features=out_features, model_name=model_name, kwargs=kwargs,
-    )
+    """``gn(name)(in_features, out_features)`` -> layer module."""
+    if model_name == "GINConv":
+        def make_gin(in_features, out_features):
+            return _conv.GINConv(apply_func=torch.nn.Linear(in_features, out_features), aggregator_type="sum")
+        return make_gin
+
+    def make(in_features, out_features):
+        return GN(in_features, out_features, model_name=model_name, kwargs=kwargs)
+    return make

@@ -86,8 +86,15 @@ def _accepts_act(mod):
 
 
 class SequentialMix(torch.nn.Module):
-    """Mixed-layer variant (pinot/representation/sequential.py:257-366) restricted to the layer
-    types implemented here (GraphConv, SAGEConv) plus activation / dropout entries."""
+    """Mixed-layer variant (pinot/representation/sequential.py:257-366): the config is a flat list of
+    strings, a layer-type keyword followed by its parameters in the order of the reference's
+    ``layer_param_type`` table (:108-128), e.g. ``["GraphConv", "32", "activation", "tanh", "TAGConv", "64",
+    "2", "dropout", "0.1"]``.  Layer types on the CSR kernels: GraphConv, SAGEConv (mean), GINConv (Linear
+    apply function, sum), SGConv, TAGConv; the others the reference's table names (GATConv, EdgeConv,
+    RelGraphConv, GatedGraphConv, ChebConv) need per-edge attention / relation kernels that are outside
+    SURVEY.md section 8 and raise NotImplementedError."""
+
+    LAYER_PARAMS = {"GraphConv": (), "SAGEConv": (), "GINConv": (), "SGConv": ("k",), "TAGConv": ("k",)}
 
     def __init__(self, config, feature_units=117, input_units=128, model_kwargs={}, input_transform=True):
         super(SequentialMix, self).__init__()
@@ -102,13 +109,20 @@ class SequentialMix(torch.nn.Module):
         config = list(config)
         while i < len(config):
             name = config[i]
-            if name in ("GraphConv", "SAGEConv"):
+            if name in self.LAYER_PARAMS:
                 out = int(config[i + 1])
-                kw = {"aggregator_type": "mean"} if name == "SAGEConv" else {}
-                setattr(self, "conv" + str(idx), getattr(_conv, name)(last, out, **kw))
+                extra = self.LAYER_PARAMS[name]
+                kw = {k: int(config[i + 2 + j]) for j, k in enumerate(extra)}
+                if name == "SAGEConv":
+                    kw["aggregator_type"] = "mean"
+                if name == "GINConv":
+                    layer = _conv.GINConv(apply_func=torch.nn.Linear(last, out), aggregator_type="sum")
+                else:
+                    layer = getattr(_conv, name)(last, out, **kw)
+                setattr(self, "conv" + str(idx), layer)
                 self.exes.append("conv" + str(idx))
                 last = out
-                i += 2
+                i += 2 + len(extra)
             elif name == "activation":
                 setattr(self, "act" + str(idx), getattr(torch, config[i + 1]))
                 self.exes.append("act" + str(idx))
@@ -119,7 +133,8 @@ class SequentialMix(torch.nn.Module):
                 i += 2
             else:
                 raise NotImplementedError(
-                    "SequentialMix layer type %r is outside the B200 hot path (GraphConv / SAGEConv only)" % (name,))
+                    "SequentialMix layer type %r is outside the B200 hot path (available: %s, activation, dropout)"
+                    % (name, ", ".join(self.LAYER_PARAMS)))
             idx += 1
         self.dummy_output = torch.nn.Linear(1, last)
 

@@ -2,8 +2,9 @@
 
 It exists for hosts that can pass buffers to this library but cannot get new device memory when
 they call it (a plug-in inside a runtime that owns the GPU's memory pool, a loop that may not
-trigger cudaMalloc's device-wide synchronisation).  Both entry points run the same kernels and
-differ only in where the deferred diagonal blocks are parked, so their outputs must agree; two calls
+trigger cudaMalloc's device-wide synchronisation).  The two entry points compute the same
+factorisation on different schedules (this one: the plain two-launches-per-panel sweep with its
+deferred diagonal blocks parked in the library's built-in array), so their outputs must agree; two calls
 in a row (a large problem, then a small one) check that contents left in the built-in array by one
 call cannot leak into the next.  Collected last on purpose (file name), and self-contained so that
 it also passes alone in a fresh process.
