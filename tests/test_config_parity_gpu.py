@@ -10,13 +10,20 @@ cancelling sums: hyper-parameter gradients, variances of near-duplicates, the il
 variational covariance at n = 4096), it passes when it is at least as close to the fp64 value as the
 fp32 reference is.  Every comparison prints both distances, so the log shows which clause held.
 
-Tolerances (north_star): embeddings, predictive mean and variance 1e-4 relative (element-wise, with
-entries below FLOOR x the largest entry measured against that floor: a sum readout entry or a
-variance that cancels to ~0 has no meaningful relative error), NLL 1e-3, gradients 5e-3 norm-wise.
+Tolerances (north_star): embeddings, predictive mean and variance 1e-4 relative, NLL 1e-3, gradients
+5e-3 norm-wise.  "Relative" is asserted twice: norm-wise at 1e-5 (embeddings) / 1e-4, and element-wise at
+1e-4 with every entry measured against max(|reference entry|, FLOOR * largest |reference entry|),
+FLOOR = 1e-2.  Why a floor at all: an embedding is a sum of ~25 tanh outputs of magnitude <= 1 per
+column, so an entry a hundred times smaller than the largest one is the remainder of a cancellation and
+fp32 itself cannot hold it to 1e-4 -- the fp32 reference sits 6e-5 ... 2.4e-4 from the fp64 values under
+a 1e-3 floor (measured on the B200 box, round 2), i.e. the reference fails its own bar there.  Each
+comparison prints the fp32 reference's own distance from fp64 under the same measure.
+
+All comparisons of a test are evaluated and printed before the test fails, so one GPU run shows the
+whole table.
 """
 import math
 
-import psutil
 import pytest
 import torch
 
@@ -30,7 +37,8 @@ from oracle import gp_ref, net_ref
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
 CONFIG = [128, "tanh", 128, "tanh", 128, "tanh"]
-FLOOR = 1e-3   # element-wise relative errors are measured against max(|ref|, FLOOR * max|ref|)
+FLOOR = 1e-2   # element-wise relative errors are measured against max(|ref|, FLOOR * max|ref|)
+FAILS = []     # comparisons that missed their bar in the running test (asserted empty at its end)
 
 
 def ref_graph(g):
@@ -47,7 +55,8 @@ def close(name, ours, ref32, ref64, tol, elementwise=False):
     noise = err(ref32, ref64)
     print("%-34s vs fp32 oracle %.2e | vs fp64 oracle %.2e | fp32 oracle vs fp64 %.2e | tol %.0e"
           % (name, e32, e64, noise, tol))
-    assert e32 < tol or e64 <= max(tol, noise), (name, e32, e64, noise, tol)
+    if not (e32 < tol or e64 <= max(tol, noise)):
+        FAILS.append((name, e32, e64, noise, tol))
     return e32, e64, noise
 
 
@@ -56,7 +65,15 @@ def scalar_close(name, ours, ref32, ref64, tol):
     scale = max(1.0, abs(ref64))
     e32, e64, noise = abs(ours - ref32) / scale, abs(ours - ref64) / scale, abs(ref32 - ref64) / scale
     print("%-34s %.6f | fp32 oracle %.6f | fp64 oracle %.6f | tol %.0e" % (name, ours, ref32, ref64, tol))
-    assert e32 < tol or e64 <= max(tol, noise), (name, ours, ref32, ref64)
+    if not (e32 < tol or e64 <= max(tol, noise)):
+        FAILS.append((name, ours, ref32, ref64, tol))
+
+
+@pytest.fixture(autouse=True)
+def _collect_failures():
+    FAILS.clear()
+    yield
+    assert not FAILS, "comparisons outside their bar: %r" % (FAILS,)
 
 
 def make_net(layer, head, kernel=None, **head_kw):
@@ -67,12 +84,25 @@ def make_net(layer, head, kernel=None, **head_kw):
     return pb.Net(rep, output_regressor_class=head, **kw)
 
 
-def oracle_exact(g, y, g_te, state, kernel, dtype):
-    """Loss, embeddings, all gradients and the predictive mean / covariance from the oracle."""
+def oracle_exact(g, y, g_te, state, kernel, dtype, chunked=False):
+    """Loss, embeddings, all gradients and the predictive mean / covariance from the oracle.
+    ``chunked``: the GP half through oracle.gp_ref.exact_gp_fit_chunked (the reference arithmetic with the
+    Gram matrix built and differentiated 256 rows at a time: at N = 4 200 the unchunked (N, N, 128) tensors
+    need ~80 GB of host memory, which the GPU box does not reliably have free)."""
     p = {k: v.detach().clone().to(dtype).requires_grad_(True) for k, v in state.items()}
     rg = ref_graph(g)
-    loss, h = net_ref.exact_net_loss(rg, y.to(dtype), p, CONFIG, kernel=kernel)
-    loss.sum().backward()
+    if chunked:
+        assert kernel == "rbf"
+        h = net_ref.representation(rg, p, CONFIG)
+        gp = "output_regressor."
+        loss, gr = gp_ref.exact_gp_fit_chunked(h.detach(), y.to(dtype), p[gp + "kernel.scale"].detach(),
+                                               p[gp + "kernel.variance"].detach(), p[gp + "log_sigma"].detach())
+        h.backward(gr["x"])
+        p[gp + "kernel.scale"].grad, p[gp + "kernel.variance"].grad = gr["scale"], gr["variance"]
+        p[gp + "log_sigma"].grad = gr["log_sigma"]
+    else:
+        loss, h = net_ref.exact_net_loss(rg, y.to(dtype), p, CONFIG, kernel=kernel)
+        loss.sum().backward()
     out = {"loss": loss.detach(), "h": h.detach(), "grads": {k: v.grad for k, v in p.items()}}
     if g_te is not None:
         with torch.no_grad():
@@ -82,7 +112,7 @@ def oracle_exact(g, y, g_te, state, kernel, dtype):
     return out
 
 
-def run_exact_config(n_mol, kernel, n_test, fp64=True):
+def run_exact_config(n_mol, kernel, n_test, fp64=True, chunked=False):
     torch.manual_seed(0)
     g, y = synthetic.make_batch(n_mol, seed=2666)
     g_te = synthetic.make_batch(n_test, seed=4242)[0] if n_test else None
@@ -92,8 +122,8 @@ def run_exact_config(n_mol, kernel, n_test, fp64=True):
         net.output_regressor.kernel.scale.fill_(-3.0)
     state = {k: v.detach().clone() for k, v in net.state_dict().items()}
     okernel = "matern52_safe" if kernel == "matern52" else "rbf"   # identical forward, finite gradients
-    o32 = oracle_exact(g, y, g_te, state, okernel, torch.float32)
-    o64 = oracle_exact(g, y, g_te, state, okernel, torch.float64) if fp64 else o32
+    o32 = oracle_exact(g, y, g_te, state, okernel, torch.float32, chunked)
+    o64 = oracle_exact(g, y, g_te, state, okernel, torch.float64, chunked) if fp64 else o32
 
     net = net.to(DEV)
     gd, yd = g.to(DEV), y.to(DEV)
@@ -128,13 +158,10 @@ def test_c1_esol_shape_matches_oracle(kernel):
     run_exact_config(1128, kernel, n_test=200)
 
 
-def test_c2_4200_molecules_one_step_matches_fp32_oracle():
-    """configs[1] / C2 (the bench workload): 4 200 molecules, one loss + backward against the fp32
-    oracle.  The reference arithmetic materialises (N, N, 128) fp32 tensors (9 GB each, several alive
-    through autograd), so the oracle needs ~80 GB of host memory and about 20-40 s."""
-    if psutil.virtual_memory().available < 90 * 2 ** 30:
-        pytest.skip("the fp32 oracle at N = 4200 needs ~80 GB of host memory")
-    run_exact_config(4200, "rbf", n_test=0, fp64=False)
+def test_c2_4200_molecules_one_step_matches_oracle():
+    """configs[1] / C2 (the bench workload): 4 200 molecules, one loss + backward against the oracle in
+    fp32 and fp64, the GP half row-chunked (same arithmetic per element, see oracle_exact)."""
+    run_exact_config(4200, "rbf", n_test=0, chunked=True)
 
 
 @pytest.mark.parametrize("n_batch", [64, 4096])

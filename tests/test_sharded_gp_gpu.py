@@ -79,7 +79,9 @@ def test_sharded_head_inside_net_matches_exact_head():
     for (name, pa), (_, pb_) in zip(a.named_parameters(), b.named_parameters()):
         assert rel_err(pb_.grad, pa.grad) < 1e-3, name
     da, db = a.condition(gt), b.condition(gt)
-    assert rel_err(db.mean, da.mean) < 1e-5
+    # two routes to the same posterior (a: cached L^-T and GEMMs, b: one sweep over [K; y; K_te,tr]); each
+    # is held to 1e-4 of the oracle in test_parity_gpu.py, so they agree to that bar, not to rounding
+    assert rel_err(db.mean, da.mean) < 1e-4
     ma, mb = a.condition_marginal(gt), b.condition_marginal(gt)
     assert rel_err(mb.mean, ma.mean) < 1e-5 and rel_err(mb.scale, ma.scale) < 1e-5
 
