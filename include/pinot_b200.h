@@ -176,9 +176,16 @@ PINOT_B200_API int pinot_b200_gram_bwd(int kind, const float* x, const float* y,
  * they must FOLLOW the dense rows).  diag_out (n, optional) receives diag(L).  *info (device int)
  * is 0 on success or 1 + the first non-positive pivot (LAPACK convention).  workspace (16-byte
  * aligned, workspace_bytes long) must hold at least pinot_b200_potrf_workspace_bytes(n) bytes; when
- * it holds pinot_b200_potrf_tma_scratch_bytes(n, n_ext_dense) MORE, the rank-512 trailing updates of
- * large factorisations (n >= 6144) run on the TMA-fed tensor-core kernel from hi / lo panel copies
- * kept in that tail (same arithmetic, same results).
+ * it holds pinot_b200_potrf_tma_scratch_bytes(n, n_ext_dense) MORE, the faster schedule for that size
+ * runs (same arithmetic, results equal up to the order of fp32 additions):
+ *   n < 6144:  with PINOT_B200_SWEEP=persistent in the environment the whole sweep is ONE persistent
+ *              cooperative kernel (csrc/chol_sweep.cu; the tail holds its progress flags) instead of one
+ *              launch per 64-column panel -- opt-in, it is not the faster of the two yet;
+ *   n >= 6144: the rank-512 trailing updates run on the TMA-fed tensor-core kernel from hi / lo panel
+ *              copies kept in the tail.
+ * The single-launch sweep is a cooperative launch: it occupies up to two CTAs per SM of the whole GPU and
+ * its CTAs wait on one another, so it needs the device to itself for its duration (a concurrent kernel
+ * on another stream delays its start rather than breaking it).
  * Replaces torch.cholesky + torch.triangular_solve at gaussian_process_regressor.py:108-119,215,373-390.
  * --------------------------------------------------------------------------------------------- */
 PINOT_B200_API int64_t pinot_b200_potrf_workspace_bytes(int64_t n);

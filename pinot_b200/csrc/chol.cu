@@ -16,6 +16,7 @@
 #include "gemm.cuh"
 #include "gemm_params.cuh"
 #include "chol_diag.cuh"
+#include "chol_sweep.cuh"
 #include <stdlib.h>
 #include "../../include/pinot_b200.h"
 #include <math.h>
@@ -338,6 +339,8 @@ int64_t pinot_b200_potrf_workspace_bytes(int64_t n) {
 
 int64_t pinot_b200_potrf_tma_scratch_bytes(int64_t n, int64_t n_ext_dense) {
     if (n < 0 || n_ext_dense < 0) return -1;
+    // small and medium n: flags of the single-launch sweep (chol_sweep.cu)
+    if (pb::sweep_persistent_applicable(n, 2 * n + n_ext_dense)) return pb::sweep_persistent_flag_bytes(n, n_ext_dense);
     const int64_t W = outer_block_width(n);
     if (W <= NB || !pb::gemm_tma_enabled()) return 0;   // single-level sweep: no rank-W updates
     // tile counter + hi / lo copies of one (n + n_ext_dense) x W panel
@@ -369,8 +372,16 @@ int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, i
             pb::aligned16(workspace))
             tma_scratch = reinterpret_cast<float*>(static_cast<char*>(workspace) + base_bytes);
     }
-    PB_CUDA(cudaMemsetAsync(flags, 0, sizeof(int) * nblk, stream));
     const int64_t r_total = n_ext_dense + (ext_identity ? n : 0);
+    // One persistent cooperative kernel for the whole sweep when the caller's workspace has room for its flags
+    // (the tail that pinot_b200_potrf_tma_scratch_bytes reports) and the rows are 16-byte aligned.
+    if (pb::sweep_persistent_enabled() && pb::sweep_persistent_applicable(n, n + r_total) && (ld % 4 == 0) && pb::aligned16(e) && pb::aligned16(workspace) &&
+        workspace_bytes >= base_bytes + pb::sweep_persistent_flag_bytes(n, n_ext_dense)) {
+        int* sflags = reinterpret_cast<int*>(static_cast<char*>(workspace) + base_bytes);
+        return pb::launch_sweep_persistent(e, ld, n, n_ext_dense, ext_identity, diag_out, wdiag, winv, sflags, info,
+                                           stream);
+    }
+    PB_CUDA(cudaMemsetAsync(flags, 0, sizeof(int) * nblk, stream));
     // the fused look-ahead kernel is built for 16-byte aligned rows only (ld % 4 == 0)
     const bool lookahead = lookahead_enabled() && (ld % 4 == 0) && pb::aligned16(e);
     // With the tensor-core GEMM the panel solve of block b+1 is fused into the update that also

@@ -22,7 +22,7 @@ extern "C" {
 
 const char* pinot_b200_last_error(void) { return pb::g_last_error; }
 
-int pinot_b200_abi_version(void) { return 3; }
+int pinot_b200_abi_version(void) { return 4; }
 
 int64_t pinot_b200_launch_count(void) { return (int64_t)__atomic_load_n(&pb::g_launches, __ATOMIC_RELAXED); }
 

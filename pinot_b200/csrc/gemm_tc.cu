@@ -257,7 +257,9 @@ __global__ void __launch_bounds__(NTHREADS, BN == 128 ? 2 : 1) tgemm_kernel(cons
 
     PB_STAMP(0);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dyn_smem) + 127) & ~(uintptr_t)127);
+    // aligned by OFFSET, not by rounding the pointer through an integer: an integer round trip drops the shared
+    // address space and every access to the operand / staging buffers becomes a generic LD / ST instead of LDS / STS
+    uint8_t* smem = dyn_smem + ((128u - (smem_u32(dyn_smem) & 127u)) & 127u);
 
     // ---- one-time setup: mbarriers + TMEM allocation ----
     if (tid == 0) {

@@ -96,7 +96,8 @@ tgemm_tma_kernel(const KParams p, const TileGrid tg, int* __restrict__ tile_coun
 
     const int ntiles = tg.count();
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dyn_smem) + 1023) & ~(uintptr_t)1023);
+    // aligned by offset so that the pointer keeps its shared address space (LDS / STS instead of generic LD / ST)
+    uint8_t* smem = dyn_smem + ((1024u - (tc::s32(dyn_smem) & 1023u)) & 1023u);
     float* epi_smem = reinterpret_cast<float*>(smem + NSTAGE * STAGE_BYTES);
 
     if (tid == 0) {

@@ -34,12 +34,14 @@ def test_library_exports_every_declared_symbol():
 
 def test_loader_and_pure_host_entry_points():
     lib = _lib.load()
-    assert lib.pinot_b200_abi_version() == 3
+    assert lib.pinot_b200_abi_version() == 4
     assert _lib.potrf_workspace_bytes(0) == 0
     # two column blocks: L11 + L11^-T per block, plus the (256-byte rounded) flag array
     assert _lib.potrf_workspace_bytes(65) == 2 * 2 * 64 * 64 * 4 + 256
-    # the TMA scratch tail exists only where the sweep runs rank-512 outer updates (n >= 6144)
-    assert _lib.potrf_workspace_bytes(4200, 1) == _lib.potrf_workspace_bytes(4200)
+    # workspace tail: below n = 6144 the flags of the single-launch sweep (one progress counter per 128-row tile of
+    # the largest stacked matrix, 2n + r rows, plus 64 ints), from there on the hi / lo panel copies of the
+    # rank-512 TMA-fed updates
+    assert _lib.potrf_workspace_bytes(4200, 1) - _lib.potrf_workspace_bytes(4200) == 4 * ((8401 + 127) // 128 + 64)
     assert _lib.potrf_workspace_bytes(8192, 1) - _lib.potrf_workspace_bytes(8192) == 256 + 2 * 8193 * 512 * 4
     assert _lib.gp_nll_grad_workspace_bytes(100) == 0
     assert _lib.gp_nll_grad_workspace_bytes(4200) == 256 + 2 * 4200 * 4200 * 4

@@ -358,6 +358,60 @@ def test_potrf_two_level_sweep_with_and_without_tma_scratch():
     assert rel_err(l.t() @ w, torch.eye(n, dtype=torch.float64, device=DEV)) < 1e-4
 
 
+@pytest.mark.parametrize("n,r,ident", [(1000, 3, 1), (4200, 1, 1), (1128, 1, 1), (129, 0, 1), (64, 2, 0), (777, 900, 0),
+                                       (2050, 5, 1), (5000, 1, 0)])
+def test_single_launch_sweep_matches_launch_per_panel_sweep(n, r, ident):
+    """PINOT_B200_SWEEP=persistent (and a workspace with the flag tail) selects the persistent cooperative kernel
+    (csrc/chol_sweep.cu) below n = 6144; otherwise the sweep runs one launch per panel.  Same arithmetic,
+    different order of the fp32 additions: they must agree to rounding, and the factor must reproduce the matrix."""
+    import os
+    from pinot_b200 import _lib
+    from pinot_b200._lib import call, ptr
+    g = torch.Generator().manual_seed(n + r)
+    a = torch.randn(n, 96, generator=g).to(DEV)
+    k = a @ a.t() / 96 + 1.5 * torch.eye(n, device=DEV)
+    ld = ops._pad4(n)
+    rows = n + r + (n if ident else 0)
+    e0 = torch.zeros(rows, ld, device=DEV)
+    e0[:n, :n] = torch.tril(k) + 123.0 * torch.triu(torch.ones(n, n, device=DEV), 1)   # junk above the diagonal
+    e0[n:n + r, :n] = torch.randn(r, n, generator=g).to(DEV)
+    if ident:
+        e0[n + r:, :n].diagonal().fill_(1.0)
+    outs, diags = [], []
+    assert _lib.potrf_workspace_bytes(n, r) > _lib.potrf_workspace_bytes(n)
+    for tail in (False, True):
+        nbytes = _lib.potrf_workspace_bytes(n, r)
+        ws = torch.empty(nbytes // 4, device=DEV)
+        e = e0.clone()
+        info = torch.full((1,), -3, dtype=torch.int32, device=DEV)
+        diag = torch.empty(n, device=DEV)
+        saved = os.environ.get("PINOT_B200_SWEEP")
+        os.environ["PINOT_B200_SWEEP"] = "persistent" if tail else "launch"
+        try:
+            for _ in range(2):                      # twice: stale flags in the workspace must not matter
+                e.copy_(e0)
+                call("potrf_ext", ptr(e), ld, n, r, ident, ptr(diag), ptr(ws), nbytes, ptr(info))
+        finally:
+            if saved is None:
+                os.environ.pop("PINOT_B200_SWEEP", None)
+            else:
+                os.environ["PINOT_B200_SWEEP"] = saved
+        assert int(info.item()) == 0
+        outs.append(e)
+        diags.append(diag)
+    lo, hi = outs
+    assert rel_err(torch.tril(hi[:n, :n]), torch.tril(lo[:n, :n])) < 2e-6
+    assert rel_err(diags[1], diags[0]) < 2e-6
+    assert torch.equal(torch.triu(hi[:n, :n], 1), torch.triu(e0[:n, :n], 1)), "the strict upper triangle is not touched"
+    if r:
+        assert rel_err(hi[n:n + r, :n], lo[n:n + r, :n]) < 1e-5
+    if ident:
+        assert rel_err(hi[n + r:, :n], lo[n + r:, :n]) < 1e-5
+        assert torch.count_nonzero(torch.tril(hi[n + r:, :n], -1)) == 0
+    l = torch.tril(hi[:n, :n]).double()
+    assert rel_err(l @ l.t(), k.double()) < 1e-5
+
+
 def test_gp_nll_grad_tma_workspace_route_matches_register_route():
     from pinot_b200 import _lib
     from pinot_b200._lib import call, ptr
