@@ -148,13 +148,23 @@ PINOT_B200_API int pinot_b200_sgemm_nt_presplit(int64_t M, int64_t N, int64_t K,
  * out[i,j] = K(x_i, y_j) + (i == j) * (diag_add + (diag_add_log ? exp(*diag_add_log) : 0)):
  * the fused `_perturb` (gaussian_process_regressor.py:29-46, rectangular matrices included) and
  * noise term exp(log_sigma) * I (:103-105).
- * lower_only != 0: 64 x 64 tiles strictly above the main diagonal are skipped (left untouched) -- for a
- * symmetric matrix that goes straight into the Cholesky sweep, which reads the lower triangle only.
+ * lower_only != 0: whole tiles (64 x 64 or 128 x 128) strictly above the main diagonal are skipped (left
+ * untouched) -- for a symmetric matrix that goes straight into the Cholesky sweep, which reads the lower
+ * triangle only.
+ * Two routes, same values to within the 1e-4 parity bar:
+ *   - workspace == NULL (or too small, or n, n2 < 256, or d > 256): CUDA cores, distances accumulated from
+ *     explicit differences exactly like the reference;
+ *   - workspace of pinot_b200_gram_workspace_bytes(...) bytes, 16-byte aligned: the dot products run as a
+ *     TMA-fed tcgen05 GEMM (3xTF32) over rows that are centred, scaled and split once; the epilogue turns
+ *     |x|^2 + |y|^2 - 2 x.y into the kernel value and recomputes in difference form every pair whose squared
+ *     distance is too small against the norms for the GEMM form to hold (csrc/gram_tc.cu).
  * --------------------------------------------------------------------------------------------- */
+PINOT_B200_API int64_t pinot_b200_gram_workspace_bytes(int64_t n, int64_t n2, int64_t d, int same_operand,
+                                                       int backward, int need_dy);
 PINOT_B200_API int pinot_b200_gram_fwd(int kind, const float* x, const float* y, const float* scale,
                         int64_t scale_len, const float* variance, float* out, int64_t ldo, int64_t n,
                         int64_t n2, int64_t d, float diag_add, const float* diag_add_log, int lower_only,
-                        cudaStream_t stream);
+                        void* workspace, int64_t workspace_bytes, cudaStream_t stream);
 /* Backward of the Gram matrix given dk = dLoss/dK (n x n2).  Outputs (any may be NULL, all are
  * overwritten): dx (n x d), dy (n2 x d), dscale (scale_len), dvariance (1).  symmetric = 1 promises
  * x == y and dk == dk^T: only the row-side pass runs and the caller doubles dx and dscale.
@@ -162,11 +172,15 @@ PINOT_B200_API int pinot_b200_gram_fwd(int kind, const float* x, const float* y,
  * row-side pass only; doubled dx is the full gradient of those rows, doubled dscale sums to the full
  * gradient over all row blocks.
  * Replaces autograd through torch.norm / exp at kernels/rbf.py:31-53 (sub-gradient 0 at d = 0).
- * Limit: d <= 256. */
+ * Limit: d <= 256.  With a workspace (pinot_b200_gram_workspace_bytes(n, n2, d, x == y, 1, need_dy), need_dy =
+ * symmetric == 0 && (dy || dscale)) the tensor-core route runs: the coefficient matrix c_ij = dk_ij k'(d_ij) / d_ij
+ * comes out of the same GEMM + epilogue as the forward pass and dx = rowsum(c) * xs - c ys is a second GEMM;
+ * near pairs (where that difference of products cancels) are added in difference form. */
 PINOT_B200_API int pinot_b200_gram_bwd(int kind, const float* x, const float* y, const float* scale,
                         int64_t scale_len, const float* variance, const float* dk, int64_t ldk,
                         int64_t n, int64_t n2, int64_t d, float* dx, float* dy, float* dscale,
-                        float* dvariance, int symmetric, cudaStream_t stream);
+                        float* dvariance, int symmetric, void* workspace, int64_t workspace_bytes,
+                        cudaStream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Kernel (4): blocked Cholesky sweep over the stacked matrix e = [A ; X], (n + r) x n, ld >= n:

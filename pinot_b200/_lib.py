@@ -36,8 +36,10 @@ SIGNATURES = {
     "pinot_b200_sgemm_nt_tma": [_i64, _i64, _i64, _f32, _ptr, _i64, _ptr, _i64, _f32, _ptr, _i64, _ptr, _i64, _ptr],
     "pinot_b200_tf32_split": [_ptr, _i64, _i64, _i64, _ptr, _i32, _ptr, _ptr, _ptr],
     "pinot_b200_sgemm_nt_presplit": [_i64, _i64, _i64, _f32, _ptr, _ptr, _ptr, _ptr, _f32, _ptr, _i64, _i32, _ptr, _ptr],
-    "pinot_b200_gram_fwd": [_i32, _ptr, _ptr, _ptr, _i64, _ptr, _ptr, _i64, _i64, _i64, _i64, _f32, _ptr, _i32, _ptr],
-    "pinot_b200_gram_bwd": [_i32, _ptr, _ptr, _ptr, _i64, _ptr, _ptr, _i64, _i64, _i64, _i64, _ptr, _ptr, _ptr, _ptr, _i32, _ptr],
+    "pinot_b200_gram_workspace_bytes": [_i64, _i64, _i64, _i32, _i32, _i32],
+    "pinot_b200_gram_fwd": [_i32, _ptr, _ptr, _ptr, _i64, _ptr, _ptr, _i64, _i64, _i64, _i64, _f32, _ptr, _i32, _ptr, _i64, _ptr],
+    "pinot_b200_gram_bwd": [_i32, _ptr, _ptr, _ptr, _i64, _ptr, _ptr, _i64, _i64, _i64, _i64, _ptr, _ptr, _ptr, _ptr, _i32, _ptr, _i64,
+                            _ptr],
     "pinot_b200_potrf_workspace_bytes": [_i64],
     "pinot_b200_potrf_tma_scratch_bytes": [_i64, _i64],
     "pinot_b200_potrf_ext": [_ptr, _i64, _i64, _i64, _i32, _ptr, _ptr, _i64, _ptr, _ptr],
@@ -53,6 +55,7 @@ SIGNATURES = {
 _RESTYPES = {
     "pinot_b200_last_error": ctypes.c_char_p,
     "pinot_b200_potrf_workspace_bytes": ctypes.c_int64,
+    "pinot_b200_gram_workspace_bytes": ctypes.c_int64,
     "pinot_b200_sgemm_nt_tma_workspace_bytes": ctypes.c_int64,
     "pinot_b200_potrf_tma_scratch_bytes": ctypes.c_int64,
     "pinot_b200_csr_build_workspace_bytes": ctypes.c_int64,
@@ -145,3 +148,9 @@ def potrf_workspace_bytes(n, n_ext_dense=None):
 
 def gp_nll_grad_workspace_bytes(n):
     return int(load().pinot_b200_gp_nll_grad_workspace_bytes(int(n)))
+
+
+def gram_workspace_bytes(n, n2, d, same, backward, need_dy=False):
+    """Scratch of the tensor-core Gram route (0: the CUDA-core route will run)."""
+    return int(load().pinot_b200_gram_workspace_bytes(int(n), int(n2), int(d), int(bool(same)), int(bool(backward)),
+                                                      int(bool(need_dy))))

@@ -337,14 +337,25 @@ int64_t pinot_b200_potrf_workspace_bytes(int64_t n) {
     return (int64_t)sizeof(float) * nblk * NB * NB * 2 + pb::ceil_div(nblk * (int64_t)sizeof(int), 256) * 256;
 }
 
-int64_t pinot_b200_potrf_tma_scratch_bytes(int64_t n, int64_t n_ext_dense) {
-    if (n < 0 || n_ext_dense < 0) return -1;
-    // small and medium n: flags of the single-launch sweep (chol_sweep.cu)
-    if (pb::sweep_persistent_applicable(n, 2 * n + n_ext_dense)) return pb::sweep_persistent_flag_bytes(n, n_ext_dense);
+}  // extern "C"
+
+namespace {
+// hi / lo panel copies of the rank-W trailing updates (two-level sweep only: n >= 6144)
+int64_t tma_panel_scratch_bytes(int64_t n, int64_t n_ext_dense) {
     const int64_t W = outer_block_width(n);
     if (W <= NB || !pb::gemm_tma_enabled()) return 0;   // single-level sweep: no rank-W updates
     // tile counter + hi / lo copies of one (n + n_ext_dense) x W panel
     return (int64_t)sizeof(float) * (pb::TMA_COUNTER_FLOATS + 2 * (n + n_ext_dense) * W);
+}
+}  // namespace
+
+extern "C" {
+
+int64_t pinot_b200_potrf_tma_scratch_bytes(int64_t n, int64_t n_ext_dense) {
+    if (n < 0 || n_ext_dense < 0) return -1;
+    // small and medium n: flags of the single-launch sweep (chol_sweep.cu); large n: the panel copies
+    if (pb::sweep_persistent_applicable(n, 2 * n + n_ext_dense)) return pb::sweep_persistent_flag_bytes(n, n_ext_dense);
+    return tma_panel_scratch_bytes(n, n_ext_dense);
 }
 
 int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, int ext_identity,
@@ -367,7 +378,7 @@ int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, i
     // optional tail of the workspace: hi / lo panel copies for the TMA-fed rank-W updates
     float* tma_scratch = nullptr;
     {
-        const int64_t extra = pinot_b200_potrf_tma_scratch_bytes(n, n_ext_dense);
+        const int64_t extra = tma_panel_scratch_bytes(n, n_ext_dense);     // NOT the flag tail of the single-launch sweep
         if (extra > 0 && workspace_bytes >= base_bytes + extra && (ld % 4 == 0) && pb::aligned16(e) &&
             pb::aligned16(workspace))
             tma_scratch = reinterpret_cast<float*>(static_cast<char*>(workspace) + base_bytes);

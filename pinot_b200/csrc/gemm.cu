@@ -266,7 +266,7 @@ int gemm(const GemmParams& g, cudaStream_t stream) {
     PB_REQUIRE(g.splitk >= 1 && g.splitk <= 65535, "gemm: bad splitk");
     // tall-and-skinny products (one row per atom, N and K <= 128): the persistent TMA-fed kernel
     if (g.K > 0 && node_gemm_applicable(g)) return launch_node_gemm(g, stream);
-    KParams p;
+    KParams p{};
     p.M = g.M; p.N = g.N; p.K = g.K;
     p.A = g.A; p.lda = g.lda; p.B = g.B; p.ldb = g.ldb; p.C = g.C; p.ldc = g.ldc;
     p.alpha = g.alpha; p.beta = g.beta; p.alpha_dev = g.alpha_dev; p.bias = g.bias; p.act = g.act;

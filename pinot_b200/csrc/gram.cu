@@ -10,6 +10,7 @@
 // parity bar.  The reference materialises an (N, N', D) tensor; here each 64x64 output tile streams
 // D through shared memory once and K is written exactly once.
 #include "common.cuh"
+#include "gram_tc.cuh"
 #include "../../include/pinot_b200.h"
 
 namespace {
@@ -301,10 +302,16 @@ int launch_bwd(int kind, const float* x, const float* y, const float* scale, int
 
 extern "C" {
 
+int64_t pinot_b200_gram_workspace_bytes(int64_t n, int64_t n2, int64_t d, int same_operand, int backward, int need_dy) {
+    if (n < 0 || n2 < 0 || d <= 0) return -1;
+    if (!pb::gram_tc_applicable(n, n2, d, backward != 0)) return 0;
+    return (int64_t)sizeof(float) * pb::gram_tc_workspace_floats(n, n2, d, same_operand != 0, backward != 0, need_dy != 0);
+}
+
 int pinot_b200_gram_fwd(int kind, const float* x, const float* y, const float* scale,
                         int64_t scale_len, const float* variance, float* out, int64_t ldo, int64_t n,
                         int64_t n2, int64_t d, float diag_add, const float* diag_add_log, int lower_only,
-                        cudaStream_t stream) {
+                        void* workspace, int64_t workspace_bytes, cudaStream_t stream) {
     PB_REQUIRE(kind == 0 || kind == 1, "gram_fwd: kind must be 0 (RBF) or 1 (Matern52)");
     PB_REQUIRE(n >= 0 && n2 >= 0 && d > 0 && d < (1 << 20), "gram_fwd: invalid sizes");
     PB_REQUIRE(scale_len == 1 || scale_len == d, "gram_fwd: scale must have 1 or d entries");
@@ -312,6 +319,11 @@ int pinot_b200_gram_fwd(int kind, const float* x, const float* y, const float* s
     PB_REQUIRE(x && y && scale && variance && out && ldo >= n2, "gram_fwd: null pointer or ldo < n2");
     const int vec_in = pb::aligned16(x) && pb::aligned16(y) && (d % 4 == 0);
     const int vec_out = pb::aligned16(out) && (ldo % 4 == 0);
+    // tensor-core route: needs the scratch of pinot_b200_gram_workspace_bytes and 16-byte aligned rows
+    if (workspace && pb::gram_tc_applicable(n, n2, d, false) && vec_out && pb::aligned16(workspace) &&
+        workspace_bytes >= pinot_b200_gram_workspace_bytes(n, n2, d, (x == y && n == n2) ? 1 : 0, 0, 0))
+        return pb::gram_fwd_tc(kind, x, y, scale, scale_len == 1 ? 0 : 1, variance, out, ldo, n, n2, (int)d, diag_add,
+                               diag_add_log, lower_only, static_cast<float*>(workspace), stream);
     dim3 grid((unsigned)pb::ceil_div(n2, TS), (unsigned)pb::ceil_div(n, TS));
     PB_REQUIRE(grid.y <= 65535, "gram_fwd: too many rows for one launch");
     gram_fwd_kernel<<<grid, 256, 0, stream>>>(kind, x, y, scale, scale_len == 1 ? 0 : 1, variance, out, ldo,
@@ -322,21 +334,30 @@ int pinot_b200_gram_fwd(int kind, const float* x, const float* y, const float* s
 int pinot_b200_gram_bwd(int kind, const float* x, const float* y, const float* scale,
                         int64_t scale_len, const float* variance, const float* dk, int64_t ldk,
                         int64_t n, int64_t n2, int64_t d, float* dx, float* dy, float* dscale,
-                        float* dvariance, int symmetric, cudaStream_t stream) {
+                        float* dvariance, int symmetric, void* workspace, int64_t workspace_bytes,
+                        cudaStream_t stream) {
     PB_REQUIRE(kind == 0 || kind == 1, "gram_bwd: kind must be 0 (RBF) or 1 (Matern52)");
     PB_REQUIRE(n >= 0 && n2 >= 0 && d > 0, "gram_bwd: invalid sizes");
     PB_REQUIRE(d <= 256, "gram_bwd: feature dimension %lld exceeds the supported maximum of 256", (long long)d);
     PB_REQUIRE(scale_len == 1 || scale_len == d, "gram_bwd: scale must have 1 or d entries");
     PB_REQUIRE(symmetric >= 0 && symmetric <= 2, "gram_bwd: symmetric must be 0, 1 or 2");
     PB_REQUIRE(symmetric != 1 || (n == n2 && x == y), "gram_bwd: symmetric mode needs x == y");
-    if (dx) PB_CUDA(cudaMemsetAsync(dx, 0, sizeof(float) * n * d, stream));
-    if (dy) PB_CUDA(cudaMemsetAsync(dy, 0, sizeof(float) * n2 * d, stream));
+    const bool tc_route = workspace && n > 0 && n2 > 0 && x && y && pb::gram_tc_applicable(n, n2, d, true) && dx &&
+                          pb::aligned16(workspace) && pb::aligned16(dk) && (ldk % 4 == 0) &&
+                          workspace_bytes >= pinot_b200_gram_workspace_bytes(n, n2, d, (x == y && n == n2) ? 1 : 0, 1,
+                                                                             (symmetric == 0 && (dy || dscale)) ? 1 : 0) &&
+                          (symmetric != 0 || dy);
+    if (dx && !tc_route) PB_CUDA(cudaMemsetAsync(dx, 0, sizeof(float) * n * d, stream));
+    if (dy && !tc_route) PB_CUDA(cudaMemsetAsync(dy, 0, sizeof(float) * n2 * d, stream));
     if (dscale) PB_CUDA(cudaMemsetAsync(dscale, 0, sizeof(float) * scale_len, stream));
     if (dvariance) PB_CUDA(cudaMemsetAsync(dvariance, 0, sizeof(float), stream));
     if (n == 0 || n2 == 0) return pb::PB_OK;
     PB_REQUIRE(x && y && scale && variance && dk && ldk >= n2, "gram_bwd: null pointer or ldk < n2");
     const int vec_in = pb::aligned16(x) && pb::aligned16(y) && (d % 4 == 0);
     const int ss = scale_len == 1 ? 0 : 1;
+    if (tc_route)
+        return pb::gram_bwd_tc(kind, x, y, scale, ss, variance, dk, ldk, n, n2, (int)d, dx, dy, dscale, dvariance, symmetric,
+                               static_cast<float*>(workspace), stream);
     auto run = [&](const float* a, const float* b, int trans, int64_t na, int64_t nb, float* da,
                    float* dsc, float* dvar) -> int {
         if (d <= 32) return launch_bwd<32>(kind, a, b, scale, ss, variance, dk, ldk, trans, na, nb, (int)d, da, dsc, dvar, vec_in, stream);

@@ -169,8 +169,11 @@ def gram_raw(kind, x, y, scale, variance, out=None, ldo=None, diag_add=0.0, diag
     if out is None:
         out = torch.empty((n, n2), device=x.device, dtype=torch.float32)
         ldo = n2
+    same = x.data_ptr() == y.data_ptr() and n == n2
+    ws_bytes = _lib.gram_workspace_bytes(n, n2, d, same, False)        # 0: small problem, CUDA-core route
+    ws = torch.empty((ws_bytes // 4,), device=x.device, dtype=torch.float32) if ws_bytes else None
     call("gram_fwd", KIND[kind], ptr(x), ptr(y), ptr(scale), scale.numel(), ptr(variance), ptr(out), ldo, n, n2, d,
-         float(diag_add), ptr(diag_add_log), int(bool(lower_only)))
+         float(diag_add), ptr(diag_add_log), int(bool(lower_only)), ptr(ws), ws_bytes)
     return out
 
 
@@ -184,8 +187,12 @@ def gram_bwd_raw(kind, x, y, scale, variance, dk, need_x=True, need_y=True, need
     dscale = torch.empty((scale.numel(),), device=dev, dtype=torch.float32) if need_scale else None
     dvar = torch.empty((1,), device=dev, dtype=torch.float32) if need_var else None
     dk = _f32c(dk)
+    same = x.data_ptr() == y.data_ptr() and n == n2
+    need_dy = (not symmetric) and (dy is not None or dscale is not None)
+    ws_bytes = _lib.gram_workspace_bytes(n, n2, d, same, True, need_dy) if (dx is not None and (symmetric or dy is not None)) else 0
+    ws = torch.empty((ws_bytes // 4,), device=dev, dtype=torch.float32) if ws_bytes else None
     call("gram_bwd", KIND[kind], ptr(x), ptr(y), ptr(scale), scale.numel(), ptr(variance), ptr(dk), dk.shape[1], n,
-         n2, d, ptr(dx), ptr(dy), ptr(dscale), ptr(dvar), int(symmetric))
+         n2, d, ptr(dx), ptr(dy), ptr(dscale), ptr(dvar), int(symmetric), ptr(ws), ws_bytes)
     return dx, dy, dscale, dvar
 
 
@@ -363,11 +370,12 @@ def exact_gp_posterior(x_te, x_tr, y_tr, scale, variance, log_sigma, kind="rbf",
 
 class ExactGPPosterior:
     """Training-set factorisation kept for repeated prediction: one sweep over
-    ``[K + (eps + sigma^2) I ; y^T ; I]`` gives ``z = L^-1 y`` and ``W = L^-T``; every later batch of
-    test points then costs one Gram launch, one GEMM ``V = K_te,tr W`` and one fused row reduction
-    (mean ``V z``, variance ``k** - |V_i|^2``) -- no n_te x n_te covariance, no second factorisation.
-    Equals the mean and the diagonal of the covariance of
-    pinot/regressors/gaussian_process_regressor.py:168-233, rectangular ``_perturb`` included."""
+    ``[K + (eps + sigma^2) I ; y^T]`` gives ``L`` and ``z = L^-1 y``; every later batch of test points then costs one
+    Gram launch, one triangular solve ``V = K_te,tr L^-T`` against the cached factor (the same arithmetic as the
+    reference's ``triangular_solve``, gaussian_process_regressor.py:215) and one fused row reduction (mean ``V z``,
+    variance ``k** - |V_i|^2``) -- no second factorisation and, for the marginals, no n_te x n_te covariance.
+    Equals the mean and (the diagonal of) the covariance of gaussian_process_regressor.py:168-233, rectangular
+    ``_perturb`` included."""
 
     @torch.no_grad()
     def __init__(self, x_tr, y_tr, scale, variance, log_sigma, kind="rbf", check=True):
@@ -379,17 +387,22 @@ class ExactGPPosterior:
         self.variance = _f32c(variance.detach().reshape(1))
         ls = _f32c(log_sigma.detach().reshape(1))
         self.ld = ld = _pad4(n)
-        e = torch.zeros((2 * n + 1, ld), device=dev, dtype=torch.float32)
+        e = torch.zeros((n + 1, ld), device=dev, dtype=torch.float32)
         gram_raw(kind, self.x_tr, self.x_tr, self.scale, self.variance, out=e, ldo=ld, diag_add=EPSILON, diag_add_log=ls,
                  lower_only=True)
         e[n, :n] = _f32c(y_tr.detach().reshape(-1))
-        e[n + 1:, :n].diagonal().fill_(1.0)
-        potrf_ext_raw(e, n, n_ext_dense=1, ext_identity=True, want_diag=False, check=check)
+        potrf_ext_raw(e, n, n_ext_dense=1, ext_identity=False, want_diag=False, check=check)
         self.z = e[n, :n].clone()
-        self.linv_t = e[n + 1:]          # (n, ld) view: W = L^-T, upper triangular
-        self.alpha = torch.empty((n,), device=dev, dtype=torch.float32)   # (K + sigma^2 I)^-1 y = W z
-        call("gemv_rows", ptr(self.linv_t), ld, n, n, 1, ptr(self.z), ptr(self.alpha))
-        self._e = e
+        self.l = e                       # rows 0..n-1: L (lower triangle)
+
+    def _solved_rows(self, x_te, row_offset=0):
+        """``V = (K_te,tr + eps I_rect) L^-T`` for a batch of test points, (n_te, n)."""
+        n = self.n
+        g = gram_raw(self.kind, x_te, self.x_tr, self.scale, self.variance)
+        if row_offset < n:   # _perturb of the rectangular K_te,tr: eps on its GLOBAL main diagonal (:95)
+            g.diagonal(offset=int(row_offset)).add_(EPSILON)
+        call("trsm_rlt", ptr(self.l), self.ld, n, ptr(g), n, g.shape[0])
+        return g
 
     @torch.no_grad()
     def mean_var(self, x_te, chunk=32768, row_offset=0):
@@ -402,34 +415,28 @@ class ExactGPPosterior:
         var = torch.empty((nte,), device=dev, dtype=torch.float32)
         for r0 in range(0, nte, chunk):
             r1 = min(nte, r0 + chunk)
-            g = gram_raw(self.kind, x_te[r0:r1], self.x_tr, self.scale, self.variance)
-            if row_offset + r0 < n:   # _perturb of the rectangular K_te,tr: eps on its main diagonal (:95)
-                g.diagonal(offset=int(row_offset) + r0).add_(EPSILON)
-            v = torch.empty((r1 - r0, n), device=dev, dtype=torch.float32)
-            call("sgemm", 0, 0, r1 - r0, n, n, 1.0, ptr(g), n, ptr(self.linv_t), self.ld, 0.0, ptr(v), n)
-            # variance from V (the mean V z of the same pass is discarded: the mean is taken as
-            # K_te,tr alpha in plain fp32, exactly the reference's expression at :212)
-            scratch = torch.empty((r1 - r0,), device=dev, dtype=torch.float32)
+            v = self._solved_rows(x_te[r0:r1], row_offset + r0)
             call("gp_predict_mean_var", ptr(v), n, r1 - r0, n, ptr(self.z), ptr(self.variance), EPSILON,
-                 ptr(scratch), ptr(var[r0:r1]))
-            call("gemv_rows", ptr(g), n, r1 - r0, n, 0, ptr(self.alpha), ptr(mean[r0:r1]))
+                 ptr(mean[r0:r1]), ptr(var[r0:r1]))
         return mean, var
-
 
     @torch.no_grad()
     def mean_cov(self, x_te):
         """Predictive mean (n_te,) and full covariance (n_te, n_te) from the cached factor:
         ``V = K_te,tr L^-T``, ``cov = K_te,te - V V^T`` (gaussian_process_regressor.py:212-221; symmetric by
-        construction)."""
+        construction; its diagonal equals ``mean_var``'s variance bit for bit)."""
         x_te = _f32c(x_te.detach())
         nte, n, dev = x_te.shape[0], self.n, x_te.device
-        g = gram_raw(self.kind, x_te, self.x_tr, self.scale, self.variance, diag_add=EPSILON)
-        v = torch.empty((nte, n), device=dev, dtype=torch.float32)
-        call("sgemm", 0, 0, nte, n, n, 1.0, ptr(g), n, ptr(self.linv_t), self.ld, 0.0, ptr(v), n)
+        v = self._solved_rows(x_te)
         mean = torch.empty((nte,), device=dev, dtype=torch.float32)
-        call("gemv_rows", ptr(g), n, nte, n, 0, ptr(self.alpha), ptr(mean))
+        var = torch.empty((nte,), device=dev, dtype=torch.float32)
+        call("gp_predict_mean_var", ptr(v), n, nte, n, ptr(self.z), ptr(self.variance), EPSILON, ptr(mean), ptr(var))
         cov = gram_raw(self.kind, x_te, x_te, self.scale, self.variance, diag_add=EPSILON)
         call("sgemm", 0, 1, nte, nte, n, -1.0, ptr(v), n, ptr(v), n, 1.0, ptr(cov), nte)
+        # The diagonal is a difference of nearly equal numbers (k** - |V_i|^2, often 10x smaller than either): it
+        # takes the row reduction's value, summed in fp32 FMAs in one pass, instead of the tensor-core GEMM's
+        # (3xTF32 products accumulated with truncation: ~1e-5 of |V_i|^2, i.e. ~1e-4 of a small variance).
+        cov.diagonal().copy_(var)
         return mean, cov
 
 

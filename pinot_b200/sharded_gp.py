@@ -74,8 +74,10 @@ class CudaKernels:
         dx = torch.empty_like(x_rows)
         dscale = torch.empty((sc.numel(),), device=dev, dtype=torch.float32) if need_scale else None
         dvar = torch.empty((1,), device=dev, dtype=torch.float32) if need_var else None
+        ws_bytes = _lib.gram_workspace_bytes(n, x_all.shape[0], d, False, True, False)
+        ws = torch.empty((ws_bytes // 4,), device=dev, dtype=torch.float32) if ws_bytes else None
         call("gram_bwd", ops.KIND[kind], ptr(x_rows), ptr(x_all), ptr(sc), sc.numel(), ptr(var), ptr(dk_rows),
-             dk_rows.stride(0), n, x_all.shape[0], d, ptr(dx), None, ptr(dscale), ptr(dvar), 2)
+             dk_rows.stride(0), n, x_all.shape[0], d, ptr(dx), None, ptr(dscale), ptr(dvar), 2, ptr(ws), ws_bytes)
         return dx, dscale, dvar
 
 

@@ -7,8 +7,11 @@ pinot/regressors/gaussian_process_regressor.py:85-233 and :346-508) and in fp64 
 the same expressions).  A quantity passes when it is within the stated tolerance of the fp32
 reference; where the reference's own fp32 rounding noise is larger than that tolerance (long
 cancelling sums: hyper-parameter gradients, variances of near-duplicates, the ill-conditioned
-variational covariance at n = 4096), it passes when it is at least as close to the fp64 value as the
-fp32 reference is.  Every comparison prints both distances, so the log shows which clause held.
+variational covariance at n = 4096, the posterior at C1 whose K + sigma^2 I has condition number ~2e4), it
+passes when it is as close to the fp64 value as the fp32 reference is, give or take a factor of two (two
+fp32 evaluations with different operation orders have independent errors of the same size: "never worse
+than the other one" would be a coin flip).  Every comparison prints all three distances, so the log shows
+which clause held.
 
 Tolerances (north_star): embeddings, predictive mean and variance 1e-4 relative, NLL 1e-3, gradients
 5e-3 norm-wise.  "Relative" is asserted twice: norm-wise at 1e-5 (embeddings) / 1e-4, and element-wise at
@@ -55,7 +58,7 @@ def close(name, ours, ref32, ref64, tol, elementwise=False):
     noise = err(ref32, ref64)
     print("%-34s vs fp32 oracle %.2e | vs fp64 oracle %.2e | fp32 oracle vs fp64 %.2e | tol %.0e"
           % (name, e32, e64, noise, tol))
-    if not (e32 < tol or e64 <= max(tol, noise)):
+    if not (e32 < tol or e64 <= max(tol, 2.0 * noise)):
         FAILS.append((name, e32, e64, noise, tol))
     return e32, e64, noise
 
@@ -65,7 +68,7 @@ def scalar_close(name, ours, ref32, ref64, tol):
     scale = max(1.0, abs(ref64))
     e32, e64, noise = abs(ours - ref32) / scale, abs(ours - ref64) / scale, abs(ref32 - ref64) / scale
     print("%-34s %.6f | fp32 oracle %.6f | fp64 oracle %.6f | tol %.0e" % (name, ours, ref32, ref64, tol))
-    if not (e32 < tol or e64 <= max(tol, noise)):
+    if not (e32 < tol or e64 <= max(tol, 2.0 * noise)):
         FAILS.append((name, ours, ref32, ref64, tol))
 
 
@@ -146,6 +149,8 @@ def run_exact_config(n_mol, kernel, n_test, fp64=True, chunked=False):
         with torch.no_grad():
             dist = net.condition(g_te.to(DEV))
             marg = net.condition_marginal(g_te.to(DEV))
+        close("predictive mean (norm-wise)", dist.mean, o32["mean"], o64["mean"], 1e-4)
+        close("predictive variance (norm-wise)", dist.variance, o32["var"], o64["var"], 1e-4)
         close("predictive mean (element-wise)", dist.mean, o32["mean"], o64["mean"], 1e-4, elementwise=True)
         close("predictive variance (element-wise)", dist.variance, o32["var"], o64["var"], 1e-4, elementwise=True)
         close("marginal mean (element-wise)", marg.mean, o32["mean"], o64["mean"], 1e-4, elementwise=True)

@@ -281,6 +281,107 @@ def test_gram_backward_same_argument(kind):
     assert torch.isfinite(xd.grad).all()
 
 
+def _embedding_like(n, d, seed, offset=3.0, spread=1.0):
+    """Rows with a large common component (like sum-pooled tanh embeddings: |x| >> typical distance), exact
+    duplicates and near-duplicates -- the inputs on which the GEMM form of the distance loses its digits."""
+    g = torch.Generator().manual_seed(seed)
+    x = offset + spread * torch.randn(n, d, generator=g)
+    x[5] = x[2]                                   # exact duplicate
+    x[9] = x[4] + 1e-4 * torch.randn(d, generator=g)   # near duplicates at several scales
+    x[11] = x[4] + 1e-2 * torch.randn(d, generator=g)
+    x[17] = x[6] + 1e-6
+    return x
+
+
+@pytest.mark.parametrize("kind", ["rbf", "matern52"])
+@pytest.mark.parametrize("n,n2,d,scale", [(700, 700, 128, -3.0), (1128, 300, 128, -1.0), (300, 1500, 32, -2.0),
+                                          (513, 513, 100, 0.0), (260, 257, 8, -1.0), (2304, 2304, 128, -3.0)])
+def test_gram_forward_tensor_core_route(kind, n, n2, d, scale, monkeypatch):
+    """The tcgen05 route (csrc/gram_tc.cu) on small and ragged shapes (forced: by default it starts at ~2000^2
+    pairs, below which the CUDA-core kernel is faster; (2304, 2304) takes it unforced).  Against the fp64 difference-form reference, 1e-4
+    element-wise (entries below 1e-6 of the largest measured against that floor), including exact and near
+    duplicates where |x|^2 + |y|^2 - 2 x.y cancels, and against the CUDA-core route."""
+    from pinot_b200 import _lib
+    from pinot_b200._lib import call, ptr
+    if n * n2 < 4000000:
+        monkeypatch.setenv("PINOT_B200_GRAM", "tc")     # read by the library on every call
+    x = _embedding_like(n, d, n + d)
+    y = x if n == n2 else _embedding_like(n2, d, n2 + d + 1)
+    if n != n2:
+        y[:40] = x[:40]                            # duplicates across the two arguments
+    sc, var = _kernel_params(kind, d, scale, 0.4)
+    want = gp_ref.KERNELS[kind](x.double(), y.double(), sc.double(), var.double())
+    xd, yd = x.to(DEV), (x.to(DEV) if n == n2 else y.to(DEV))
+    if n == n2:
+        yd = xd
+    assert _lib.gram_workspace_bytes(n, n2, d, n == n2, False) > 0
+    got = ops.gram_raw(kind, xd, yd, sc.to(DEV), var.to(DEV).reshape(1), diag_add=1e-5)
+    want_p = gp_ref.perturb(want)
+    assert max_rel_err(got, want_p) < 1e-4
+    assert rel_err(got, want_p) < 1e-6
+    # the CUDA-core route (no workspace) on the same inputs
+    ffma = torch.empty((n, n2), device=DEV)
+    scd, vard = sc.to(DEV).reshape(-1).contiguous(), var.to(DEV).reshape(1)     # kept alive across the launch
+    call("gram_fwd", ops.KIND[kind], ptr(xd), ptr(yd), ptr(scd), scd.numel(), ptr(vard), ptr(ffma), n2, n, n2, d, 1e-5, None, 0,
+         None, 0)
+    assert max_rel_err(got, ffma) < 1e-4
+    if n == n2:
+        assert torch.allclose(torch.diagonal(got).cpu(), (torch.exp(var) + 1e-5).expand(n), rtol=1e-6)
+        # lower_only writes whole tiles on or below the diagonal and leaves the rest alone
+        lo = torch.full((n, n), -7.0, device=DEV)
+        ops.gram_raw(kind, xd, xd, sc.to(DEV), var.to(DEV).reshape(1), out=lo, ldo=n, diag_add=1e-5, lower_only=True)
+        assert torch.equal(torch.tril(lo), torch.tril(got))
+        assert float(lo[0, n - 1]) == -7.0
+
+
+@pytest.mark.parametrize("kind", ["rbf", "matern52"])
+@pytest.mark.parametrize("n,n2,d,scale,same", [(600, 600, 128, -3.0, True), (400, 900, 64, -2.0, False),
+                                               (300, 300, 36, -1.0, False), (1500, 1500, 128, -3.0, True)])
+def test_gram_backward_tensor_core_route(kind, n, n2, d, scale, same, monkeypatch):
+    """Backward through the coefficient-matrix GEMMs (csrc/gram_tc.cu) against fp64 autograd of the reference
+    formula; the near pairs go through the exact fix-up, the others through rowsum(c) xs - c ys.  Forced onto
+    the tensor-core route (by default it starts at ~1200^2 pairs; (1500, 1500) takes it unforced)."""
+    if n * n2 < 1500000:
+        monkeypatch.setenv("PINOT_B200_GRAM", "tc")
+    from pinot_b200 import _lib
+    assert _lib.gram_workspace_bytes(n, n if same else n2, d, same, True, not same) > 0
+    x = _embedding_like(n, d, 3 * n + d, offset=2.0)
+    y = None if same else _embedding_like(n2, d, 5 * n2 + d, offset=2.0)
+    if not same:
+        y[:30] = x[:30]
+    sc, var = _kernel_params(kind, d, scale, 0.2)
+    g = torch.Generator().manual_seed(1)
+    gk = torch.randn(n, n if same else n2, generator=g)
+    if same:
+        gk = 0.5 * (gk + gk.t())
+    ref_kind = "matern52_safe" if kind == "matern52" else kind
+    xr, scr, varr = (t.double().requires_grad_(True) for t in (x, sc, var))
+    yr = xr if same else y.double().requires_grad_(True)
+    gp_ref.KERNELS[ref_kind](xr, yr, scr, varr).backward(gk.double())
+    xd, scd, vard = (t.to(DEV).requires_grad_(True) for t in (x, sc, var))
+    yd = None if same else y.to(DEV).requires_grad_(True)
+    ops.gram(kind, xd, yd, scd, vard).backward(gk.to(DEV))
+    # rows whose nearest neighbour sits 1e-6 ... 1e-4 away: fp32 inputs cannot resolve that difference to 1e-3 (the
+    # reference's own fp32 arithmetic cannot either); they are held to 2e-2, everything else to 1e-3
+    close = [4, 6, 9, 11, 17]
+    far = [i for i in range(n) if i not in close]
+    assert rel_err(xd.grad[far], xr.grad[far]) < 1e-3
+    assert rel_err(xd.grad[close], xr.grad[close]) < 2e-2
+    if not same:
+        assert rel_err(yd.grad, yr.grad) < 5e-3
+        assert rel_err(yd.grad[30:], yr.grad[30:]) < 1e-3
+    assert rel_err(scd.grad, scr.grad) < 5e-3
+    assert rel_err(vard.grad, varr.grad) < 1e-3
+    assert torch.isfinite(xd.grad).all()
+    # the symmetric single-pass mode used by the exact-GP loss (row pass, doubled by the caller)
+    if same:
+        dx, _, dscale, dvar = ops.gram_bwd_raw(kind, xd.detach(), xd.detach(), scd.detach().reshape(-1),
+                                               vard.detach().reshape(1), gk.to(DEV), need_y=False, symmetric=True)
+        assert rel_err(2.0 * dx[far], xr.grad[far]) < 1e-3
+        assert rel_err(2.0 * dscale.reshape(scr.shape), scr.grad) < 5e-3
+        assert rel_err(dvar.reshape(()), varr.grad) < 1e-3
+
+
 # ---------------------------------------------------------------------------------------------
 # kernel (4)
 # ---------------------------------------------------------------------------------------------
