@@ -9,7 +9,8 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpinot_b200.so")
+# PINOT_B200_LIB: another build of the same library (A/B timing of a kernel variant); the ABI check still applies
+LIB_PATH = os.environ.get("PINOT_B200_LIB") or os.path.join(_HERE, "libpinot_b200.so")
 
 _c_float_p = ctypes.c_void_p  # device pointers travel as raw addresses
 _i64 = ctypes.c_int64

@@ -609,20 +609,31 @@ int pinot_b200_trsm_rlt(const float* l, int64_t ldl, int64_t n, float* x, int64_
     PB_REQUIRE(n >= 0 && r >= 0 && ldl >= n && ldx >= n && n < (1ll << 30), "trsm_rlt: invalid sizes");
     if (n == 0 || r == 0) return pb::PB_OK;
     PB_REQUIRE(l && x, "trsm_rlt: null pointer");
-    for (int64_t c0 = 0; c0 < n; c0 += NB) {
-        const int nb = (int)((n - c0) < NB ? (n - c0) : NB);
-        const int64_t c1 = c0 + nb;
-        int rc = launch_panel(l, ldl, x, ldx, (int)c0, nb, 0, r, 1, nullptr, nullptr, stream);
-        if (rc) return rc;
-        if (c1 < n) {
-            pb::GemmParams g;
-            g.M = (int)r; g.N = (int)(n - c1); g.K = nb;
-            g.A = x + c0; g.lda = ldx; g.transA = false;
-            g.B = l + c1 * ldl + c0; g.ldb = ldl; g.transB = true;
-            g.C = x + c1; g.ldc = ldx; g.alpha = -1.f; g.beta = 1.f;
-            rc = pb::gemm(g, stream);
+    // Two levels: panels of NB columns are solved and applied inside an outer block of TRSM_OB columns; the
+    // columns to the right of the outer block are updated once per outer block with K = TRSM_OB.  With r in the
+    // tens of thousands X does not fit in L2, and a rank-NB update of everything to the right per panel would
+    // stream it n / NB times; this way it is streamed n / TRSM_OB times.
+    constexpr int64_t TRSM_OB = 512;
+    auto update = [&](int64_t k0, int64_t k1, int64_t n0, int64_t n1) -> int {
+        // X[:, n0:n1] -= X[:, k0:k1] L[n0:n1, k0:k1]^T
+        if (n1 <= n0) return pb::PB_OK;
+        pb::GemmParams g;
+        g.M = (int)r; g.N = (int)(n1 - n0); g.K = (int)(k1 - k0);
+        g.A = x + k0; g.lda = ldx; g.transA = false;
+        g.B = l + n0 * ldl + k0; g.ldb = ldl; g.transB = true;
+        g.C = x + n0; g.ldc = ldx; g.alpha = -1.f; g.beta = 1.f;
+        return pb::gemm(g, stream);
+    };
+    for (int64_t o0 = 0; o0 < n; o0 += TRSM_OB) {
+        const int64_t o1 = (o0 + TRSM_OB < n) ? o0 + TRSM_OB : n;
+        for (int64_t c0 = o0; c0 < o1; c0 += NB) {
+            const int nb = (int)((o1 - c0) < NB ? (o1 - c0) : NB);
+            int rc = launch_panel(l, ldl, x, ldx, (int)c0, nb, 0, r, 1, nullptr, nullptr, stream);
             if (rc) return rc;
+            if ((rc = update(c0, c0 + nb, c0 + nb, o1))) return rc;
         }
+        int rc = update(o0, o1, o1, n);
+        if (rc) return rc;
     }
     return pb::PB_OK;
 }
