@@ -414,6 +414,7 @@ int pinot_b200_potrf_ext(float* e, int64_t ld, int64_t n, int64_t n_ext_dense, i
         g.post_info = info;
         g.post_nb = (int)((n - c1) < NB ? (n - c1) : NB);
         g.post_c0 = (int)c1;
+        g.pdl = 1;      // every launch before this one in the sweep is a kernel: the step may be scheduled while it drains
         if (fused) {
             g.post_flag = flags + b1;
             // 2: the solve runs on the tensor cores (full 64-column blocks); 1: FFMA version

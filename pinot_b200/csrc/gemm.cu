@@ -277,7 +277,7 @@ int gemm(const GemmParams& g, cudaStream_t stream) {
     p.vecC = aligned16(g.C) && (g.ldc % 4 == 0);
     p.post_wdiag = g.post_wdiag; p.post_winv = g.post_winv; p.post_info = g.post_info;
     p.post_nb = g.post_nb; p.post_c0 = g.post_c0;
-    p.post_flag = g.post_flag; p.post_solve = g.post_solve;
+    p.post_flag = g.post_flag; p.post_solve = g.post_solve; p.pdl = g.pdl;
     PB_REQUIRE(!g.post_solve || (g.post_flag && g.post_wdiag && use_tensor_cores()),
                "gemm: the fused panel solve needs the look-ahead factor and the tensor-core kernel");
     PB_REQUIRE(!g.post_wdiag || (g.post_winv && g.splitk == 1 && g.post_nb > 0 && g.post_nb <= DIAG_NB),

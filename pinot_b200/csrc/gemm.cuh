@@ -40,6 +40,7 @@ struct GemmParams {
     // panel-TRSM launch of the next sweep step.
     int* post_flag = nullptr;
     int post_solve = 0;
+    int pdl = 0;                // the kernel before this one in the stream is the step before it in a sweep: launch as its programmatic dependent
 };
 
 // True when gemm() dispatches to the tcgen05 kernel (PINOT_B200_GEMM != "ffma").

@@ -19,6 +19,7 @@ struct KParams {
     int vecA, vecB, vecC;
     float* post_wdiag; float* post_winv; int* post_info; int post_nb, post_c0;
     int* post_flag; int post_solve;
+    int pdl;                                // launched as a programmatic dependent of the kernel before it (sweep steps)
 };
 
 // gemm_tc.cu: 3xTF32 tensor-core (tcgen05 / TMEM) implementation of the same contract.

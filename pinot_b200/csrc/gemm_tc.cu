@@ -240,6 +240,11 @@ __global__ void __launch_bounds__(NTHREADS, BN == 128 ? 2 : 1) tgemm_kernel(cons
     __shared__ __align__(8) uint64_t solve_bar;       // look-ahead kernel: completion of the panel-solve MMAs
     __shared__ uint32_t tmem_base_holder;
 
+    // Sweep steps are launched as programmatic dependents of the step before them: every CTA lets the next step's
+    // grid be scheduled at once (it takes SMs as this grid drains and does its set-up there), and no CTA touches
+    // global memory before the grid before it has completed (griddepcontrol.wait below).  Both are no-ops in a
+    // plain launch.
+    if (POST) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const int m0 = blockIdx.y * TM, n0 = blockIdx.x * BN;
     if (p.lower && n0 > m0 + TM - 1) return;
 
@@ -278,6 +283,7 @@ __global__ void __launch_bounds__(NTHREADS, BN == 128 ? 2 : 1) tgemm_kernel(cons
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_d = tmem_base_holder;
+    if (POST) asm volatile("griddepcontrol.wait;" ::: "memory");
     PB_STAMP(1);
 
     // MMA N: the valid columns of this tile rounded up to a legal UMMA N (multiple of 16)
@@ -604,6 +610,11 @@ extern "C" __attribute__((visibility("default"))) int pinot_b200_debug_times(uns
 }
 #endif
 
+static bool pdl_enabled() {
+    const char* v = getenv("PINOT_B200_PDL");          // =0: plain launches (read on every call)
+    return !(v && v[0] == '0');
+}
+
 int launch_gemm_tc(const KParams& p, bool transA, bool transB, dim3 grid, cudaStream_t stream) {
     // epilogue variant (see epilogue_rows): the generic one whenever a specialised one is not built
     int epi = 0;
@@ -617,7 +628,17 @@ int launch_gemm_tc(const KParams& p, bool transA, bool transB, dim3 grid, cudaSt
                       p.N >= 1024 && p.K >= 256;
     auto launch = [&](auto kern, int smem_bytes, dim3 g) -> int {
         PB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-        kern<<<g, NTHREADS, smem_bytes, stream>>>(p);
+        if (p.pdl && pdl_enabled()) {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = g; cfg.blockDim = dim3(NTHREADS, 1, 1); cfg.dynamicSmemBytes = (size_t)smem_bytes; cfg.stream = stream;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = attr; cfg.numAttrs = 1;
+            PB_CUDA(cudaLaunchKernelEx(&cfg, kern, p));
+        } else {
+            kern<<<g, NTHREADS, smem_bytes, stream>>>(p);
+        }
         return check_launch("gemm (tcgen05)");
     };
     if (wide) {
