@@ -72,10 +72,13 @@ def profile_json(name):
 
 
 def ncu_traffic(kernel_key):
-    """DRAM bytes (read + write) per launch of a kernel from the committed ncu --set full capture
-    (profiles/rNN/ncu_traffic.json, taken at the default workload), or None."""
+    """DRAM bytes (read + write) per call of an entry point from the committed ncu --set full capture of its
+    dominant kernel (profiles/rNN/ncu_traffic.json, taken at the default workload), or None.  ncu flushes L2
+    between launches, so this is cold-cache traffic: an upper bound on what the call moves inside the step."""
     try:
-        return float(profile_json("ncu_traffic.json")["kernels"][kernel_key]["dram_bytes_per_launch"])
+        k = profile_json("ncu_traffic.json")["kernels"][kernel_key]
+        # an entry point that is a chain of launches of one kernel (the sweep): per call, like `achieved`
+        return float(k["dram_bytes_per_launch"]) * float(k.get("launches_per_call", 1))
     except (KeyError, ValueError, TypeError):
         return None
 
