@@ -152,8 +152,9 @@ PINOT_B200_API int pinot_b200_sgemm_nt_presplit(int64_t M, int64_t N, int64_t K,
  * untouched) -- for a symmetric matrix that goes straight into the Cholesky sweep, which reads the lower
  * triangle only.
  * Two routes, same values to within the 1e-4 parity bar:
- *   - workspace == NULL (or too small, or n, n2 < 256, or d > 256): CUDA cores, distances accumulated from
- *     explicit differences exactly like the reference;
+ *   - workspace == NULL (or too small, or fewer than ~2000^2 pairs forward / ~1200^2 backward, where the
+ *     CUDA-core kernel is the faster one, or d outside 8..256): CUDA cores, distances accumulated from explicit
+ *     differences exactly like the reference; pinot_b200_gram_workspace_bytes returns 0 for these cases;
  *   - workspace of pinot_b200_gram_workspace_bytes(...) bytes, 16-byte aligned: the dot products run as a
  *     TMA-fed tcgen05 GEMM (3xTF32) over rows that are centred, scaled and split once; the epilogue turns
  *     |x|^2 + |y|^2 - 2 x.y into the kernel value and recomputes in difference form every pair whose squared
