@@ -387,25 +387,31 @@ def measure_train_step(ctx, n_mol, steps, warmup, want_e2e, sample_clocks):
         return res
 
     # ---- end-to-end: host buffers in, loss out, every step (public API) ----
-    src_h, dst_h = (t.pin_memory() for t in g_host.edges())
-    feat_h = g_host.ndata["h"].pin_memory()
-    y_h = y_host.pin_memory()
-    bnn, bne = g_host.batch_num_nodes().tolist(), g_host.batch_num_edges().tolist()
-    h2d = sum(t.numel() * t.element_size() for t in (src_h, dst_h, feat_h, y_h)) + 8 * len(bnn)
+    # The batch lives on the host the way pinot_b200.data.PackedDataset keeps it: pinned edge list and targets,
+    # atom features compact (atomic number as a byte + 17 fp16 columns, bit-exact against the dense (n, 117)
+    # matrix, checked when it is packed) and expanded on the device after the copy.
+    packed = pb.data.PackedBatch.from_graph(g_host, y_host)
+    src_h, dst_h, feat_src, y_h = packed.host_tensors()
+    feats_h = tuple(feat_src) if packed.compact else (feat_src,)
+    bnn, bne = packed.batch_num_nodes, packed.batch_num_edges
+    h2d = packed.transfer_bytes()
     copy_stream = torch.cuda.Stream(device=dev, priority=-1)   # its small kernels go ahead of the step's
     bnn_h = g_host.batch_num_nodes().to(torch.long).pin_memory()
-    stage = [tuple(torch.empty_like(t, device=dev) for t in (src_h, dst_h, feat_h, y_h, bnn_h)) for _ in range(2)]
+    host_ts = (src_h, dst_h, y_h, bnn_h) + feats_h
+    stage = [tuple(torch.empty_like(t, device=dev) for t in host_ts) for _ in range(2)]
     n_up = [0]
 
     def upload_eager():
-        """H2D of one step's inputs + graph index build, on the copy stream."""
-        s_d, d_d, f_d, y_d, b_d = stage[n_up[0] % 2]
+        """H2D of one step's inputs + feature expansion + graph index build, on the copy stream."""
+        from pinot_b200 import ops
+        dev_ts = stage[n_up[0] % 2]
         n_up[0] += 1
         with torch.cuda.stream(copy_stream):
-            for dst_t, src_t in ((s_d, src_h), (d_d, dst_h), (f_d, feat_h), (y_d, y_h), (b_d, bnn_h)):
+            for dst_t, src_t in zip(dev_ts, host_ts):
                 dst_t.copy_(src_t, non_blocking=True)
-            gs = BatchedGraph(s_d, d_d, g_host.number_of_nodes(), bnn, bne, validate=False, batch_num_nodes_device=b_d)
-            gs.ndata["h"] = f_d
+            s_d, d_d, y_d, b_d = dev_ts[:4]
+            gs = BatchedGraph(s_d, d_d, packed.num_nodes, bnn, bne, validate=False, batch_num_nodes_device=b_d)
+            gs.ndata["h"] = ops.expand_atom_features(dev_ts[4], dev_ts[5], packed.n_onehot) if packed.compact else dev_ts[4]
             gs.csr()
             ev = torch.cuda.Event()
             ev.record(copy_stream)
@@ -429,7 +435,8 @@ def measure_train_step(ctx, n_mol, steps, warmup, want_e2e, sample_clocks):
     if captured is not None:
         # ... and so is the upload: two captured H2D + index-build graphs (one per staging slot)
         try:
-            uploads = [pb.CapturedBatchUpload(src_h, dst_h, feat_h, y_h, g_host.number_of_nodes(), bnn, bne,
+            feat_arg = (feat_src[0], feat_src[1], packed.n_onehot) if packed.compact else feat_src
+            uploads = [pb.CapturedBatchUpload(src_h, dst_h, feat_arg, y_h, packed.num_nodes, bnn, bne,
                                               copy_stream, device=dev) for _ in range(2)]
             mode += " + CUDA-graph replay of the upload (pinot_b200.CapturedBatchUpload)"
 
@@ -474,8 +481,11 @@ def measure_train_step(ctx, n_mol, steps, warmup, want_e2e, sample_clocks):
     gc.enable()
     e2e = {"value": n_mol * world * steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": 4, "ms_per_step": 1e3 * e2e_s / steps, "mode": mode,
-           "includes": "per step: H2D of edges/features/targets from pinned memory + CSR build (copy stream, "
-                       "overlapping the previous step), train step, loss.item()"}
+           "includes": "per step: H2D of edges/targets/%s from pinned memory + %sCSR build (copy stream, "
+                       "overlapping the previous step), train step, loss.item()"
+                       % (("compact atom features (uint8 atomic number + %d %s columns per atom)"
+                           % (packed.fp.shape[1], str(packed.fp.dtype).replace("torch.", "")),
+                           "device-side expansion to the (n, 117) fp32 matrix + ") if packed.compact else ("dense features", ""))}
     marks = step_marks[-steps:]
     e2e["per_step_ms"] = [round(1e3 * (b - a), 3) for a, b in zip([t0] + marks[:-1], marks)]
     if captured is not None:

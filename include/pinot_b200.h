@@ -79,6 +79,16 @@ PINOT_B200_API int pinot_b200_csr_build(const int64_t* src, const int64_t* dst, 
                          int32_t* indptr_t, int32_t* indices_t, float* in_norm, float* out_norm,
                          float* inv_in_deg, int64_t* in_deg, int32_t* seg_offsets, int32_t* node_seg,
                          void* workspace, int64_t workspace_bytes, cudaStream_t stream);
+/* Atom features from their compact form: out[a, :] = one_hot(z[a], n_onehot) ++ float(fp[a, 0 .. n_fp-1]),
+ * (n_atoms x (n_onehot + n_fp)) fp32 with leading dimension ld; fp holds fp16 (fp_bytes = 2) or fp32
+ * (fp_bytes = 4) values.  The reference builds exactly this per atom on the host (one-hot of the atomic number,
+ * pinot/graph.py:163-168 / :217-222, followed by the 17 integers and flags of fp_oe / fp_rdkit, :50-69 /
+ * :108-128, concatenated at :173 / :227) and ships the dense (n, 117) fp32 matrix to the device; shipping
+ * 1 + fp_bytes * n_fp bytes per atom instead of 4 * (n_onehot + n_fp) cuts that transfer 13x (fp16) or 6.8x
+ * (fp32).  The host side (pinot_b200/data/packed.py) only uses a compact form that reproduces the dense matrix
+ * bit for bit.  Limits: n_onehot <= 256 (z is uint8), n_fp < 65536. */
+PINOT_B200_API int pinot_b200_expand_atom_features(const uint8_t* z, const void* fp, int fp_bytes, int64_t n_atoms,
+                                    int64_t n_onehot, int64_t n_fp, float* out, int64_t ld, cudaStream_t stream);
 /* Row gather out[i,:] = x[idx[i],:] (idx: int64, device).  The data movement of re-batching a
  * selection of molecules, i.e. of dgl.batch([dgl.unbatch(g)[i] for i in idxs]) in
  * pinot/active/experiment.py:83-104 (_slice_fn_graph). */

@@ -27,6 +27,7 @@ SIGNATURES = {
     "pinot_b200_mp_csr_aggregate_bwd": [_ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _i64, _ptr],
     "pinot_b200_csr_build_workspace_bytes": [_i64, _i64],
     "pinot_b200_csr_build": [_ptr, _ptr, _i64, _i64, _ptr, _i64] + [_ptr] * 10 + [_ptr, _i64, _ptr],
+    "pinot_b200_expand_atom_features": [_ptr, _ptr, _i32, _i64, _i64, _i64, _ptr, _i64, _ptr],
     "pinot_b200_gather_rows": [_ptr, _ptr, _ptr, _i64, _i64, _ptr],
     "pinot_b200_segment_readout_fwd": [_ptr, _ptr, _ptr, _i64, _i64, _i32, _ptr],
     "pinot_b200_segment_readout_bwd": [_ptr, _ptr, _ptr, _ptr, _i64, _i64, _i32, _ptr],

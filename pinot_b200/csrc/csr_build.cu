@@ -7,6 +7,7 @@
 // Counting sort: histogram -> exclusive scan -> scatter with atomic cursors (unordered inside a row) ->
 // per-row insertion sort by edge id (rows of molecular graphs hold <= 6 entries).
 #include "common.cuh"
+#include <cuda_fp16.h>
 #include "../../include/pinot_b200.h"
 
 namespace {
@@ -201,9 +202,51 @@ node_vectors_kernel(const int* __restrict__ indptr, const int* __restrict__ indp
     node_seg[i] = lo;
 }
 
+// Atom features from their compact host form (the reference builds them per atom: a one-hot of the atomic number,
+// pinot/graph.py:163-168, followed by 17 small integers / flags, :50-69 and :173): one output element per thread,
+// coalesced fp32 stores; the 1 + 2 * n_fp bytes per atom read here are re-read from L1.
+__device__ __forceinline__ float fp_value(const __half* p) { return __half2float(__ldg(p)); }
+__device__ __forceinline__ float fp_value(const float* p) { return __ldg(p); }
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+expand_atom_features_kernel(const uint8_t* __restrict__ z, const T* __restrict__ fp, int64_t n_atoms, int n_onehot, int n_fp,
+                            float* __restrict__ out, int64_t ld) {
+    const int width = n_onehot + n_fp;
+    const int64_t total = n_atoms * width;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t a = i / width;
+        const int c = (int)(i - a * width);
+        float v;
+        if (c < n_onehot) v = (__ldg(z + a) == c) ? 1.f : 0.f;
+        else v = fp_value(fp + a * n_fp + (c - n_onehot));
+        out[a * ld + c] = v;
+    }
+}
+
 }  // namespace
 
 extern "C" {
+
+int pinot_b200_expand_atom_features(const uint8_t* z, const void* fp, int fp_bytes, int64_t n_atoms, int64_t n_onehot,
+                                    int64_t n_fp, float* out, int64_t ld, cudaStream_t stream) {
+    PB_REQUIRE(n_atoms >= 0 && n_onehot >= 0 && n_onehot <= 256 && n_fp >= 0 && n_fp < (1 << 16) && ld >= n_onehot + n_fp,
+               "expand_atom_features: invalid sizes");
+    PB_REQUIRE(fp_bytes == 2 || fp_bytes == 4, "expand_atom_features: fp_bytes must be 2 (fp16) or 4 (fp32)");
+    if (n_atoms == 0 || n_onehot + n_fp == 0) return pb::PB_OK;
+    PB_REQUIRE(out && (n_onehot == 0 || z) && (n_fp == 0 || fp), "expand_atom_features: null pointer");
+    const int64_t total = n_atoms * (n_onehot + n_fp);
+    const int64_t blocks = pb::ceil_div(total, 256);
+    const unsigned grid = (unsigned)(blocks < 148 * 16 ? blocks : 148 * 16);
+    if (fp_bytes == 2)
+        expand_atom_features_kernel<__half><<<grid, 256, 0, stream>>>(z, static_cast<const __half*>(fp), n_atoms, (int)n_onehot,
+                                                                      (int)n_fp, out, ld);
+    else
+        expand_atom_features_kernel<float><<<grid, 256, 0, stream>>>(z, static_cast<const float*>(fp), n_atoms, (int)n_onehot,
+                                                                     (int)n_fp, out, ld);
+    return pb::check_launch("expand_atom_features");
+}
+
 
 int64_t pinot_b200_csr_build_workspace_bytes(int64_t n_nodes, int64_t n_edges) {
     if (n_nodes < 0 || n_edges < 0) return -1;

@@ -504,5 +504,16 @@ def chol_solve(k, b, check=True, info_sink=None):
     return _CholSolve.apply(k, b, check, info_sink)
 
 
+def expand_atom_features(z, fp, n_onehot=100):
+    """Dense ``(n_atoms, n_onehot + n_fp)`` fp32 atom features from their compact form (uint8 atomic number,
+    fp16 or fp32 fingerprint columns): what pinot/graph.py:163-173 builds per atom on the host."""
+    assert z.is_cuda and fp.is_cuda and z.dtype == torch.uint8 and fp.dtype in (torch.float16, torch.float32)
+    z, fp = z.contiguous(), fp.contiguous()
+    n, n_fp = z.shape[0], (fp.shape[1] if fp.dim() == 2 else 0)
+    out = torch.empty((n, n_onehot + n_fp), device=z.device, dtype=torch.float32)
+    call("expand_atom_features", ptr(z), ptr(fp), fp.element_size(), n, n_onehot, n_fp, ptr(out), n_onehot + n_fp)
+    return out
+
+
 def log_2pi():
     return math.log(2.0 * math.pi)
