@@ -109,6 +109,46 @@ def main():
         ms = timeit(lambda: ops.cholesky(k.clone() if False else k), iters=5, flush=flush)
         out.append({"kernel": "potrf (sweep, no extension rows)", "N": n, "ms": ms,
                     "TFLOPs": n ** 3 / 3.0 / ms / 1e9, "frac_bf16_peak": n ** 3 / 3.0 / ms / 1e9 / tf})
+        # the loss's sweep: stacked [K; y^T; I] (factor + z + L^-T), raw entry point
+        from pinot_b200 import _lib
+        from pinot_b200._lib import call, ptr
+        ld = ops._pad4(n)
+        e0 = torch.zeros(2 * n + 1, ld, device=DEV)
+        e0[:n, :n] = k
+        e0[n, :n] = y.flatten()
+        e0[n + 1:, :n].diagonal().fill_(1.0)
+        e = e0.clone()
+        nbytes = _lib.potrf_workspace_bytes(n, 1)
+        ws = torch.empty(nbytes // 4, device=DEV)
+        info = torch.zeros(1, dtype=torch.int32, device=DEV)
+
+        def sweep():
+            call("potrf_ext", ptr(e), ld, n, 1, 1, None, ptr(ws), nbytes, ptr(info))
+
+        def restore():
+            e.copy_(e0)
+
+        ts = []
+        for _ in range(6):
+            restore()
+            if flush is not None:
+                flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            sweep()
+            b.record()
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b))
+        ms = sorted(ts[1:])[len(ts[1:]) // 2]
+        out.append({"kernel": "potrf_ext [K; y; I] (factor + L^-1 y + L^-T: the loss's sweep)", "N": n, "ms": ms,
+                    "TFLOPs": (2.0 * n ** 3 / 3.0 + n * n) / ms / 1e9, "frac_bf16_peak": (2.0 * n ** 3 / 3.0 + n * n) / ms / 1e9 / tf})
+        del e, e0, ws
+        dk = torch.randn(n, n, device=DEV)
+        dk = 0.5 * (dk + dk.t())
+        ms = timeit(lambda: ops.gram_bwd_raw("rbf", x, x, sc, var.reshape(1), dk, need_y=False, symmetric=True), iters=5, flush=flush)
+        out.append({"kernel": "gram_bwd (symmetric mode, as in the loss)", "N": n, "D": d, "ms": ms,
+                    "read_GBps": 4.0 * n * n / ms / 1e6, "frac_hbm": 4.0 * n * n / ms / 1e6 / hbm})
+        del dk
         del k
         xg = x.clone().requires_grad_(True)
         lsg = ls.clone().requires_grad_(True)

@@ -28,9 +28,16 @@ namespace pb {
 
 #ifdef PB_DEBUG_TIMING
 __device__ unsigned long long g_dbg_times[16];
-#define PB_STAMP(i) do { if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); g_dbg_times[i] = t_; } } while (0)
+// per sweep step (index = first column of the block being factored / 64): the same stamps of tile (0,0), plus
+// stamp 15 = the last tile-column-0 CTA to finish its panel solve (atomicMax).  Use with PINOT_B200_PDL=0: a
+// dependent launch starts before the step before it has finished and would overwrite the step index.
+__device__ unsigned long long g_dbg_steps[512][16];
+__device__ int g_dbg_step_index;
+#define PB_STAMP(i) do { if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); g_dbg_times[i] = t_; if (g_dbg_step_index >= 0 && g_dbg_step_index < 512) g_dbg_steps[g_dbg_step_index][i] = t_; } } while (0)
+#define PB_STAMP_COL0_DONE() do { if (threadIdx.x == 0 && g_dbg_step_index >= 0 && g_dbg_step_index < 512) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); atomicMax(&g_dbg_steps[g_dbg_step_index][15], t_); } } while (0)
 #else
 #define PB_STAMP(i)
+#define PB_STAMP_COL0_DONE()
 #endif
 }  // namespace pb
 #include "chol_diag.cuh"
@@ -260,6 +267,9 @@ __global__ void __launch_bounds__(NTHREADS, BN == 128 ? 2 : 1) tgemm_kernel(cons
     }
     const int num_k = (ke > kb) ? (ke - kb + TK - 1) / TK : 0;
 
+#ifdef PB_DEBUG_TIMING
+    if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0) g_dbg_step_index = (POST && p.post_wdiag) ? p.post_c0 / 64 : -1;
+#endif
     PB_STAMP(0);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     // aligned by OFFSET, not by rounding the pointer through an integer: an integer round trip drops the shared
@@ -598,6 +608,7 @@ __global__ void __launch_bounds__(NTHREADS, BN == 128 ? 2 : 1) tgemm_kernel(cons
                 panel_solve_tile(p.C, p.ldc, m0, p.M, p.post_nb, p.post_winv, fsmem);
             }
             PB_STAMP(7);
+            PB_STAMP_COL0_DONE();
         }
     }
 }
@@ -607,6 +618,9 @@ __global__ void __launch_bounds__(NTHREADS, BN == 128 ? 2 : 1) tgemm_kernel(cons
 #ifdef PB_DEBUG_TIMING
 extern "C" __attribute__((visibility("default"))) int pinot_b200_debug_times(unsigned long long* out16) {
     return (int)cudaMemcpyFromSymbol(out16, g_dbg_times, sizeof(unsigned long long) * 16);
+}
+extern "C" __attribute__((visibility("default"))) int pinot_b200_debug_steps(unsigned long long* out512x16) {
+    return (int)cudaMemcpyFromSymbol(out512x16, g_dbg_steps, sizeof(unsigned long long) * 512 * 16);
 }
 #endif
 
