@@ -614,7 +614,13 @@ int pinot_b200_trsm_rlt(const float* l, int64_t ldl, int64_t n, float* x, int64_
     // columns to the right of the outer block are updated once per outer block with K = TRSM_OB.  With r in the
     // tens of thousands X does not fit in L2, and a rank-NB update of everything to the right per panel would
     // stream it n / NB times; this way it is streamed n / TRSM_OB times.
-    constexpr int64_t TRSM_OB = 512;
+    // The width is bounded by ACCURACY, not by traffic: the tensor core truncates when it accumulates, so the
+    // error of a K-long product grows with K / 8 MMAs (measured on the C1 posterior, worst element of the marginal
+    // variance against fp64, fp32 reference 3.6e-5: width 128 -> 5.2e-5, 256 -> 1.1e-4, 512 -> 1.8e-4).  128 keeps
+    // the posterior inside the parity bar; PINOT_B200_TRSM_OB overrides (development switch, read on every call).
+    const char* obv = getenv("PINOT_B200_TRSM_OB");
+    const int64_t ob_req = obv ? atoll(obv) : 128;
+    const int64_t TRSM_OB = (ob_req >= NB && ob_req % NB == 0) ? ob_req : 128;
     auto update = [&](int64_t k0, int64_t k1, int64_t n0, int64_t n1) -> int {
         // X[:, n0:n1] -= X[:, k0:k1] L[n0:n1, k0:k1]^T
         if (n1 <= n0) return pb::PB_OK;
