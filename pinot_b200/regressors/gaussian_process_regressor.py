@@ -232,9 +232,14 @@ class VariationalGaussianProcessRegressor(GaussianProcessRegressor):
         row-major below it (:316-332)."""
         m = self.y_tr_sigma_diag.shape[0]
         y_tr_diag = torch.diag_embed(torch.exp(self.y_tr_sigma_diag))
-        idx = torch.arange(m, device=y_tr_diag.device)
-        mask = torch.gt(idx[:, None], idx[None, :])
-        return y_tr_diag.masked_scatter(mask, self.y_tr_sigma_tril)
+        # The reference fills the strictly-lower part with masked_scatter (row-major order of the mask).  The same
+        # positions as explicit indices: masked_scatter and its backward (masked_select) read a count back from the
+        # device, which stalls the step and cannot be captured in a CUDA graph.
+        key = (m, y_tr_diag.device)
+        if getattr(self, "_tril_index_key", None) != key:
+            rows, cols = torch.tril_indices(m, m, offset=-1, device=y_tr_diag.device)      # row-major, like the mask
+            self._tril_index, self._tril_index_key = (rows, cols), key
+        return y_tr_diag.index_put(self._tril_index, self.y_tr_sigma_tril)
 
     def _gram(self, a, b=None):
         return ops.gram(self._kind(), a, b, self.kernel.scale, self.kernel.variance, self.epsilon)

@@ -82,3 +82,37 @@ def test_captured_upload_replays_follow_the_pinned_host_buffers():
         for name in ("indptr", "indices", "indptr_t", "indices_t", "seg_offsets", "node_seg", "in_norm", "inv_in_deg"):
             assert torch.equal(getattr(gd.csr(), name), getattr(want.csr(), name)), name
     up.release()
+
+
+def test_variational_gp_step_can_be_captured_and_follows_eager_training():
+    """The variational head's step holds no device->host read any more (the strictly-lower scale is filled through
+    explicit indices instead of masked_scatter): it captures, and the replay trains like the eager step."""
+    torch.manual_seed(3)
+    g, y = synthetic.make_batch(96, seed=21)
+    g, y = g.to(DEV), y.to(DEV)
+    rep = pb.representation.Sequential(pb.representation.dgl_legacy.gn("SAGEConv"), [64, "tanh", 64, "tanh"])
+    eager = pb.Net(rep, output_regressor_class=pb.regressors.VariationalGaussianProcessRegressor, n_inducing_points=64).to(DEV)
+    with torch.no_grad():
+        eager.output_regressor.kernel.scale.fill_(-2.0)
+        eager.output_regressor.y_tr_sigma_tril.normal_(0.0, 0.02)
+    captured = copy.deepcopy(eager)
+    # the explicit indices reproduce masked_scatter's layout
+    head = eager.output_regressor
+    m = head.y_tr_sigma_diag.shape[0]
+    idx = torch.arange(m, device=DEV)
+    want = torch.diag_embed(torch.exp(head.y_tr_sigma_diag)).masked_scatter(idx[:, None] > idx[None, :], head.y_tr_sigma_tril)
+    assert torch.equal(head._y_tr_sigma(), want)
+    opt_e = torch.optim.Adam(eager.parameters(), 1e-3)
+    opt_c = torch.optim.Adam(captured.parameters(), 1e-3, capturable=True)
+    step = pb.CapturedTrainStep(captured, opt_c, g, y)
+    for it in range(3):
+        opt_e.zero_grad()
+        le = eager.loss(g, y).sum()
+        le.backward()
+        opt_e.step()
+        lc = step()
+        assert abs(float(lc) - float(le)) <= 1e-4 * max(1.0, abs(float(le))), (it, float(lc), float(le))
+    captured.output_regressor.verify()
+    for pe, pc in zip(eager.parameters(), captured.parameters()):
+        assert rel_err(pc, pe) < 1e-4
+    step.release()
