@@ -489,17 +489,30 @@ def measure_train_step(ctx, n_mol, steps, warmup, want_e2e, sample_clocks):
     marks = step_marks[-steps:]
     e2e["per_step_ms"] = [round(1e3 * (b - a), 3) for a, b in zip([t0] + marks[:-1], marks)]
     if captured is not None:
-        # the same replay with resident inputs, device-timed like `value` (L2 flushed between steps)
-        ts = []
+        # The same step -- zero_grad, loss, backward, gradient all-reduce, Adam -- replayed from its CUDA graph with
+        # resident inputs: device-timed exactly like the eager loop above (CUDA events, L2 flushed between steps,
+        # barrier on both sides, max over ranks, clocks sampled).  This is the product's path for full-batch
+        # training, so it is what `value` reports; the eager loop stays in the line as ms_per_step_eager.
+        sampler2 = ClockSampler(ctx.local_rank)
+        for _ in range(3):
+            captured()
+        ctx.barrier()
+        if sample_clocks and rank == 0:
+            sampler2.start()
+        evs2 = []
         for _ in range(steps):
             flush_buf.zero_()
             s_ev, e_ev = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             s_ev.record()
             captured()
             e_ev.record()
-            torch.cuda.synchronize()
-            ts.append(s_ev.elapsed_time(e_ev))
-        e2e["captured_step_device_ms"] = ctx.max_over_ranks(sum(ts) / len(ts))
+            evs2.append((s_ev, e_ev))
+        ctx.barrier()
+        net.output_regressor.verify()
+        clocks2 = sampler2.stop() if (sample_clocks and rank == 0) else None
+        e2e["captured_step_device_ms"] = ctx.max_over_ranks(sum(a.elapsed_time(b) for a, b in evs2)) / steps
+        res["captured_ms_per_step"] = e2e["captured_step_device_ms"]
+        res["captured_clocks"] = clocks2
         captured.release()     # the graph holds the NCCL all-reduce: it must go before the process group
     if uploads is not None:
         for u in uploads:
@@ -706,14 +719,15 @@ def b200_main(args):
     c1 = None
     if world == 1 and not args.no_c1 and n_mol != N_MOL_C1:
         r1 = measure_train_step(ctx, N_MOL_C1, args.steps, args.warmup, want_e2e=not args.no_e2e, sample_clocks=False)
-        c1 = {"config": workload_config(N_MOL_C1, 1, "C1 (ESOL shape)"), "value": r1["value"], "unit": UNIT,
-              "ms_per_step": r1["ms_per_step"], "e2e": r1["e2e"], "gpu_launches": r1["launches"],
+        ms1 = r1.get("captured_ms_per_step") or r1["ms_per_step"]
+        c1 = {"config": workload_config(N_MOL_C1, 1, "C1 (ESOL shape)"), "value": N_MOL_C1 / (ms1 * 1e-3), "unit": UNIT,
+              "ms_per_step": ms1, "ms_per_step_eager": r1["ms_per_step"], "e2e": r1["e2e"], "gpu_launches": r1["launches"],
               "kernel_shares": r1["shares"], "final_loss": r1["final_loss"]}
         if not args.no_cpu_baseline:
             c = cpu_arm(N_MOL_C1, steps=5, warmup=2, budget_s=30.0)
             c1["cpu_baseline"] = {"value": c["value"], "unit": UNIT, "cores": c["cores"], "kind": "port",
                                   "sample": c["sample"], "ms_per_step": c["ms_per_step"]}
-            c1["speedup_vs_cpu_port"] = {"device": r1["value"] / c["value"],
+            c1["speedup_vs_cpu_port"] = {"device": c1["value"] / c["value"],
                                          "e2e": (r1["e2e"]["value"] / c["value"]) if r1["e2e"] else None}
 
     fit = None
@@ -740,15 +754,24 @@ def b200_main(args):
                         "ms_per_step": c["ms_per_step"], "molecules": c["molecules"]}
 
     if rank == 0:
+        cfg = workload_config(n_mol, world, "C2" if n_mol == N_MOL else "custom")
+        ms, clocks = main["ms_per_step"], main["clocks"]
+        cfg["step"] = "eager launches (one C-ABI call per kernel)"
+        if main.get("captured_ms_per_step"):
+            # same work, same timing rules, replayed from the CUDA graph (see measure_train_step)
+            ms = main["captured_ms_per_step"]
+            clocks = main.get("captured_clocks") or clocks
+            cfg["step"] = "replayed from a CUDA graph (pinot_b200.CapturedTrainStep); eager launches: ms_per_step_eager"
         line = {
-            "metric": METRIC, "value": main["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": main["ms_per_step"], "higher_is_better": True,
+            "metric": METRIC, "value": n_mol * world / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms, "ms_per_step_eager": main["ms_per_step"],
+            "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": workload_config(n_mol, world, "C2" if n_mol == N_MOL else "custom"),
+            "config": cfg,
             "roofline": rl[0] if rl else None, "roofline_other_kernels": rl[1:], "kernel_shares": main["shares"],
             "c1_esol_shape": c1, "exact_gp_fit_n16k": fit, "sharded_gp_fit": sharded, "bo_round": bo,
             "cpu_baseline": cpu_baseline, "e2e": main["e2e"], "gpu_launches": main["launches"],
-            "clocks": main["clocks"], "final_loss": main["final_loss"],
+            "clocks": clocks, "clocks_eager_loop": main["clocks"], "final_loss": main["final_loss"],
         }
         print(json.dumps(line))
     if world > 1:
