@@ -470,6 +470,12 @@ def measure_train_step(ctx, n_mol, steps, warmup, want_e2e, sample_clocks):
         return loss_host
 
     import gc
+    # clocks for the replayed-step numbers: sampled from here to the end of the device-timed replay loop below (the
+    # end-to-end loop and that loop run the same step back to back; the replay loop alone lasts ~40 ms, less than
+    # nvidia-smi needs to deliver its first sample)
+    sampler2 = ClockSampler(ctx.local_rank)
+    if sample_clocks and rank == 0:
+        sampler2.start()
     e2e_loop(5)
     gc.collect()
     gc.disable()                                     # no collector pauses inside the timed loop
@@ -493,12 +499,9 @@ def measure_train_step(ctx, n_mol, steps, warmup, want_e2e, sample_clocks):
         # resident inputs: device-timed exactly like the eager loop above (CUDA events, L2 flushed between steps,
         # barrier on both sides, max over ranks, clocks sampled).  This is the product's path for full-batch
         # training, so it is what `value` reports; the eager loop stays in the line as ms_per_step_eager.
-        sampler2 = ClockSampler(ctx.local_rank)
         for _ in range(3):
             captured()
         ctx.barrier()
-        if sample_clocks and rank == 0:
-            sampler2.start()
         evs2 = []
         for _ in range(steps):
             flush_buf.zero_()
@@ -510,10 +513,14 @@ def measure_train_step(ctx, n_mol, steps, warmup, want_e2e, sample_clocks):
         ctx.barrier()
         net.output_regressor.verify()
         clocks2 = sampler2.stop() if (sample_clocks and rank == 0) else None
+        if clocks2 is not None:
+            clocks2["window"] = "end-to-end loop + device-timed replay loop"
         e2e["captured_step_device_ms"] = ctx.max_over_ranks(sum(a.elapsed_time(b) for a, b in evs2)) / steps
         res["captured_ms_per_step"] = e2e["captured_step_device_ms"]
         res["captured_clocks"] = clocks2
         captured.release()     # the graph holds the NCCL all-reduce: it must go before the process group
+    elif sample_clocks and rank == 0:
+        sampler2.stop()
     if uploads is not None:
         for u in uploads:
             u.release()
