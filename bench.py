@@ -447,6 +447,21 @@ def measure_train_step(ctx, n_mol, steps, warmup, want_e2e, sample_clocks):
         except Exception as exc:  # noqa: BLE001
             sys.stderr.write("bench.py: CUDA-graph capture of the upload failed (%s); eager upload\n" % exc)
             uploads, upload = None, upload_eager
+    # One captured step per staging slot, reading that slot's device tensors in place: the step graph of slot i
+    # consumes what upload graph i wrote, no device-to-device copy of the batch in between (parameters and optimizer
+    # state are shared by both step graphs).
+    bound = None
+    if uploads is not None:
+        try:
+            for u in uploads:
+                _, _, ev0 = u.replay()
+                ev0.synchronize()
+            bound = [pb.CapturedTrainStep(net, opt_c, u.g, u.y, after_backward=lambda: bucket.allreduce(average=False))
+                     for u in uploads]
+            mode += ", one step graph per staging slot (no device copy of the batch)"
+        except Exception as exc:  # noqa: BLE001
+            sys.stderr.write("bench.py: per-slot step graphs failed (%s); copying into one step graph\n" % exc)
+            bound = None
     step_marks = []
 
     def e2e_loop(n_steps):
@@ -457,7 +472,9 @@ def measure_train_step(ctx, n_mol, steps, warmup, want_e2e, sample_clocks):
         for k in range(n_steps):
             gs, yy, ev = nxt
             torch.cuda.current_stream().wait_event(ev)
-            if captured is not None:
+            if bound is not None:
+                loss_dev = bound[(n_up[0] - 1) % 2]()   # the step graph that reads this slot's tensors
+            elif captured is not None:
                 captured.load(gs, yy)                # device copy into the captured inputs
                 loss_dev = captured()                # one graph launch
             else:
@@ -519,6 +536,9 @@ def measure_train_step(ctx, n_mol, steps, warmup, want_e2e, sample_clocks):
         res["captured_ms_per_step"] = e2e["captured_step_device_ms"]
         res["captured_clocks"] = clocks2
         captured.release()     # the graph holds the NCCL all-reduce: it must go before the process group
+        if bound is not None:
+            for b in bound:
+                b.release()
     elif sample_clocks and rank == 0:
         sampler2.stop()
     if uploads is not None:
