@@ -121,7 +121,9 @@ def test_select_equals_unbatch_then_batch():
     ref = dgl_ref.from_arrays(*g.edges(), g.number_of_nodes(), g.batch_num_nodes().tolist(),
                               g.batch_num_edges().tolist(), ndata={"h": g.ndata["h"]})
     ref_parts = dgl_ref.unbatch(ref)
-    for idxs in ([5], [39, 0, 17, 17, 3], list(range(40)), list(range(10, 20))):
+    # (a `range` of consecutive graphs takes the slicing fast path, the lists the general gather)
+    for idxs in ([5], [39, 0, 17, 17, 3], list(range(40)), list(range(10, 20)), range(10, 20), range(0, 40), range(39, 40),
+                 range(0, 1)):
         got = g.select(idxs)
         want = dgl_ref.batch([ref_parts[i] for i in idxs])
         assert got.edges()[0].tolist() == want.src and got.edges()[1].tolist() == want.dst
