@@ -256,6 +256,16 @@ PINOT_B200_API int pinot_b200_potrf_ext_noalloc(float* e, int64_t ld, int64_t n,
  * input=X^T, A=L, upper=False) transposed; gaussian_process_regressor.py:112-114,215,376-390). */
 PINOT_B200_API int pinot_b200_trsm_rlt(const float* l, int64_t ldl, int64_t n, float* x, int64_t ldx, int64_t r,
                         cudaStream_t stream);
+/* The same solve with caller scratch (pinot_b200_trsm_rlt_workspace_bytes(n, r) bytes, 16-byte aligned; 0 means the
+ * sizes are too small for it to pay and NULL / 0 may be passed): the updates of everything right of a 512-column
+ * block run as ONE product from pre-split operands on the TMA-fed tensor-core GEMM whose accumulators are flushed
+ * into registers every 128 K-columns -- the accuracy of 128-wide updates (the posterior's 1e-4 bar needs that: the
+ * tensor core truncates when it accumulates) with one pass over X per 512 columns.  Same values as
+ * pinot_b200_trsm_rlt to within fp32 rounding; needs ldl, ldx multiples of 4 and 16-byte aligned l, x (otherwise
+ * it falls back to the plain schedule). */
+PINOT_B200_API int64_t pinot_b200_trsm_rlt_workspace_bytes(int64_t n, int64_t r);
+PINOT_B200_API int pinot_b200_trsm_rlt_ws(const float* l, int64_t ldl, int64_t n, float* x, int64_t ldx, int64_t r,
+                           void* workspace, int64_t workspace_bytes, cudaStream_t stream);
 /* Zero the strict upper triangle of an n x n matrix (torch.cholesky's output convention). */
 PINOT_B200_API int pinot_b200_zero_upper(float* a, int64_t ld, int64_t n, cudaStream_t stream);
 /* y[i] = sum_k m[i,k] v[k] (upper != 0: only k >= i), one warp per row.  alpha = L^{-T} z

@@ -47,6 +47,8 @@ SIGNATURES = {
     "pinot_b200_potrf_ext": [_ptr, _i64, _i64, _i64, _i32, _ptr, _ptr, _i64, _ptr, _ptr],
     "pinot_b200_potrf_ext_noalloc": [_ptr, _i64, _i64, _i64, _i32, _ptr, _ptr, _ptr],
     "pinot_b200_trsm_rlt": [_ptr, _i64, _i64, _ptr, _i64, _i64, _ptr],
+    "pinot_b200_trsm_rlt_workspace_bytes": [_i64, _i64],
+    "pinot_b200_trsm_rlt_ws": [_ptr, _i64, _i64, _ptr, _i64, _i64, _ptr, _i64, _ptr],
     "pinot_b200_zero_upper": [_ptr, _i64, _i64, _ptr],
     "pinot_b200_gemv_rows": [_ptr, _i64, _i64, _i64, _i32, _ptr, _ptr, _ptr],
     "pinot_b200_gp_nll": [_ptr, _ptr, _i64, _ptr, _ptr],
@@ -58,6 +60,7 @@ _RESTYPES = {
     "pinot_b200_last_error": ctypes.c_char_p,
     "pinot_b200_potrf_workspace_bytes": ctypes.c_int64,
     "pinot_b200_gram_workspace_bytes": ctypes.c_int64,
+    "pinot_b200_trsm_rlt_workspace_bytes": ctypes.c_int64,
     "pinot_b200_sgemm_nt_tma_workspace_bytes": ctypes.c_int64,
     "pinot_b200_potrf_tma_scratch_bytes": ctypes.c_int64,
     "pinot_b200_csr_build_workspace_bytes": ctypes.c_int64,
@@ -150,6 +153,11 @@ def potrf_workspace_bytes(n, n_ext_dense=None):
 
 def gp_nll_grad_workspace_bytes(n):
     return int(load().pinot_b200_gp_nll_grad_workspace_bytes(int(n)))
+
+
+def trsm_rlt_workspace_bytes(n, r):
+    """Scratch of the triangular solve with accurate wide updates (0: the plain schedule will run)."""
+    return int(load().pinot_b200_trsm_rlt_workspace_bytes(int(n), int(r)))
 
 
 def gram_workspace_bytes(n, n2, d, same, backward, need_dy=False):

@@ -604,23 +604,14 @@ int pinot_b200_potrf_ext_noalloc(float* e, int64_t ld, int64_t n, int64_t n_ext_
     return pb::check_launch("chol_writeback (noalloc)");
 }
 
-int pinot_b200_trsm_rlt(const float* l, int64_t ldl, int64_t n, float* x, int64_t ldx, int64_t r,
-                        cudaStream_t stream) {
-    // X (r x n) <- X L^{-T}, i.e. X^T <- L^{-1} X^T, with L already factored (lower, n x n).
-    PB_REQUIRE(n >= 0 && r >= 0 && ldl >= n && ldx >= n && n < (1ll << 30), "trsm_rlt: invalid sizes");
-    if (n == 0 || r == 0) return pb::PB_OK;
-    PB_REQUIRE(l && x, "trsm_rlt: null pointer");
-    // Two levels: panels of NB columns are solved and applied inside an outer block of TRSM_OB columns; the
-    // columns to the right of the outer block are updated once per outer block with K = TRSM_OB.  With r in the
-    // tens of thousands X does not fit in L2, and a rank-NB update of everything to the right per panel would
-    // stream it n / NB times; this way it is streamed n / TRSM_OB times.
-    // The width is bounded by ACCURACY, not by traffic: the tensor core truncates when it accumulates, so the
-    // error of a K-long product grows with K / 8 MMAs (measured on the C1 posterior, worst element of the marginal
-    // variance against fp64, fp32 reference 3.6e-5: width 128 -> 5.2e-5, 256 -> 1.1e-4, 512 -> 1.8e-4).  128 keeps
-    // the posterior inside the parity bar; PINOT_B200_TRSM_OB overrides (development switch, read on every call).
-    const char* obv = getenv("PINOT_B200_TRSM_OB");
-    const int64_t ob_req = obv ? atoll(obv) : 128;
-    const int64_t TRSM_OB = (ob_req >= NB && ob_req % NB == 0) ? ob_req : 128;
+}  // extern "C"
+
+namespace {
+
+// X[:, c_beg:c_end) <- solved against L (columns before c_beg are solved and already applied to this range): panels of
+// NB columns inside outer blocks of `ob` columns; updates stay inside [c_beg, c_end).
+int trsm_range(const float* l, int64_t ldl, float* x, int64_t ldx, int64_t r, int64_t c_beg, int64_t c_end, int64_t ob,
+               cudaStream_t stream) {
     auto update = [&](int64_t k0, int64_t k1, int64_t n0, int64_t n1) -> int {
         // X[:, n0:n1] -= X[:, k0:k1] L[n0:n1, k0:k1]^T
         if (n1 <= n0) return pb::PB_OK;
@@ -631,15 +622,88 @@ int pinot_b200_trsm_rlt(const float* l, int64_t ldl, int64_t n, float* x, int64_
         g.C = x + n0; g.ldc = ldx; g.alpha = -1.f; g.beta = 1.f;
         return pb::gemm(g, stream);
     };
-    for (int64_t o0 = 0; o0 < n; o0 += TRSM_OB) {
-        const int64_t o1 = (o0 + TRSM_OB < n) ? o0 + TRSM_OB : n;
+    for (int64_t o0 = c_beg; o0 < c_end; o0 += ob) {
+        const int64_t o1 = (o0 + ob < c_end) ? o0 + ob : c_end;
         for (int64_t c0 = o0; c0 < o1; c0 += NB) {
             const int nb = (int)((o1 - c0) < NB ? (o1 - c0) : NB);
             int rc = launch_panel(l, ldl, x, ldx, (int)c0, nb, 0, r, 1, nullptr, nullptr, stream);
             if (rc) return rc;
             if ((rc = update(c0, c0 + nb, c0 + nb, o1))) return rc;
         }
-        int rc = update(o0, o1, o1, n);
+        int rc = update(o0, o1, o1, c_end);
+        if (rc) return rc;
+    }
+    return pb::PB_OK;
+}
+
+// Width of the rank-K updates of the triangular solve.  Bounded by ACCURACY, not by traffic: the tensor core
+// truncates when it accumulates, so the error of a K-long product grows with K / 8 MMAs between two flushes of the
+// accumulators (measured on the C1 posterior, worst element of the marginal variance against fp64, fp32 reference
+// 3.6e-5: width 128 -> 5.2e-5, 256 -> 1.1e-4, 512 -> 1.8e-4; profiles/r02/trsm_outer_block.md).  128 keeps the
+// posterior inside the parity bar; PINOT_B200_TRSM_OB overrides (development switch, read on every call).
+int64_t trsm_outer_block() {
+    const char* obv = getenv("PINOT_B200_TRSM_OB");
+    const int64_t ob_req = obv ? atoll(obv) : 128;
+    return (ob_req >= NB && ob_req % NB == 0) ? ob_req : 128;
+}
+
+constexpr int64_t TRSM_ACC_BLOCK = 512;     // columns per accurate rank-K update (flushed into registers every 128)
+
+}  // namespace
+
+extern "C" {
+
+int pinot_b200_trsm_rlt(const float* l, int64_t ldl, int64_t n, float* x, int64_t ldx, int64_t r,
+                        cudaStream_t stream) {
+    // X (r x n) <- X L^{-T}, i.e. X^T <- L^{-1} X^T, with L already factored (lower, n x n).
+    // Two levels: panels of NB columns are solved and applied inside an outer block; the columns to the right of the
+    // outer block are updated once per outer block.  With r in the tens of thousands X does not fit in L2, and a
+    // rank-NB update of everything to the right per panel would stream it n / NB times.
+    PB_REQUIRE(n >= 0 && r >= 0 && ldl >= n && ldx >= n && n < (1ll << 30), "trsm_rlt: invalid sizes");
+    if (n == 0 || r == 0) return pb::PB_OK;
+    PB_REQUIRE(l && x, "trsm_rlt: null pointer");
+    return trsm_range(l, ldl, x, ldx, r, 0, n, trsm_outer_block(), stream);
+}
+
+int64_t pinot_b200_trsm_rlt_workspace_bytes(int64_t n, int64_t r) {
+    if (n < 0 || r < 0) return -1;
+    if (n < 2 * TRSM_ACC_BLOCK || r < 1024 || !pb::gemm_tma_enabled()) return 0;      // the plain schedule is used
+    const int64_t n4 = (n + 3) / 4 * 4;
+    return (int64_t)sizeof(float) * (pb::TMA_COUNTER_FLOATS + 2 * n * n4 + 2 * r * TRSM_ACC_BLOCK);
+}
+
+int pinot_b200_trsm_rlt_ws(const float* l, int64_t ldl, int64_t n, float* x, int64_t ldx, int64_t r, void* workspace,
+                           int64_t workspace_bytes, cudaStream_t stream) {
+    // The same solve with the wide updates on the TMA-fed GEMM: inside 512-column blocks the schedule above; the
+    // columns to the right of a block get ONE rank-512 update from pre-split operands, accumulated in the accurate
+    // way (accumulators flushed into registers every 128 K-columns: the error of 128-wide updates, one pass over C).
+    PB_REQUIRE(n >= 0 && r >= 0 && ldl >= n && ldx >= n && n < (1ll << 30), "trsm_rlt_ws: invalid sizes");
+    if (n == 0 || r == 0) return pb::PB_OK;
+    PB_REQUIRE(l && x, "trsm_rlt_ws: null pointer");
+    const int64_t need = pinot_b200_trsm_rlt_workspace_bytes(n, r);
+    const bool fast = need > 0 && workspace && workspace_bytes >= need && ldl % 4 == 0 && ldx % 4 == 0 && pb::aligned16(l) &&
+                      pb::aligned16(x) && pb::aligned16(workspace);
+    if (!fast) return trsm_range(l, ldl, x, ldx, r, 0, n, trsm_outer_block(), stream);
+    const int64_t n4 = (n + 3) / 4 * 4;
+    float* base = static_cast<float*>(workspace);
+    float* lhi = base + pb::TMA_COUNTER_FLOATS;
+    float* llo = lhi + n * n4;
+    float* xhi = llo + n * n4;
+    float* xlo = xhi + r * TRSM_ACC_BLOCK;
+    int rc = pb::tma_split_operand(l, ldl, n, n, lhi, llo, nullptr, 0, 0, stream);
+    if (rc) return rc;
+    for (int64_t o0 = 0; o0 < n; o0 += TRSM_ACC_BLOCK) {
+        const int64_t o1 = (o0 + TRSM_ACC_BLOCK < n) ? o0 + TRSM_ACC_BLOCK : n;
+        if ((rc = trsm_range(l, ldl, x, ldx, r, o0, o1, trsm_outer_block(), stream))) return rc;
+        if (o1 >= n) break;
+        const int64_t K = o1 - o0;                        // a multiple of 4 (o1 < n here: K == TRSM_ACC_BLOCK)
+        if ((rc = pb::tma_split_operand(x + o0, ldx, r, K, xhi, xlo, nullptr, 0, 0, stream))) return rc;
+        pb::KParams p{};
+        p.M = (int)r; p.N = (int)(n - o1); p.K = (int)K;
+        p.C = x + o1; p.ldc = ldx;
+        p.alpha = -1.f; p.beta = 1.f; p.splitk = 1; p.vecC = 1;
+        rc = pb::launch_gemm_tma_presplit(p, xhi, xlo, lhi + o1 * n4 + o0, llo + o1 * n4 + o0, reinterpret_cast<int*>(base), stream,
+                                          K, n4, /*accurate=*/true);
         if (rc) return rc;
     }
     return pb::PB_OK;

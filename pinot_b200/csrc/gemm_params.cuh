@@ -33,9 +33,12 @@ bool gemm_tma_enabled();   // tensor-core GEMMs selected and PINOT_B200_TMA != 0
 // 1 = columns * colscale, 2 = columns * sqrt(colscale); tri: upper-triangular operand of a ktri product
 int tma_split_operand(const float* x, int64_t ldx, int64_t rows, int64_t K, float* hi, float* lo, const float* colscale,
                       int scale_mode, int tri, cudaStream_t stream);
-// tile_counter: one int of device scratch for the kernel's dynamic tile queue (zeroed here, on the stream)
+// tile_counter: one int of device scratch for the kernel's dynamic tile queue (zeroed here, on the stream).
+// ld_a / ld_b: leading dimensions of the pre-split arrays (0 = ceil4(K): compact); a block of a larger array is passed
+// as a pointer to its first element plus the array's leading dimension.  accurate: accumulators flushed into registers
+// every 128 K-columns (plain alpha / beta products only).
 int launch_gemm_tma_presplit(const KParams& p, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo,
-                             int* tile_counter, cudaStream_t stream);
+                             int* tile_counter, cudaStream_t stream, int64_t ld_a = 0, int64_t ld_b = 0, bool accurate = false);
 constexpr int64_t TMA_COUNTER_FLOATS = 64;   // callers reserve 256 bytes for that counter
 
 }  // namespace pb

@@ -65,7 +65,7 @@ struct TileGrid {
 struct TileWork {
     int m0, n0, kb, num_k, num_chunks;
 };
-__device__ __forceinline__ TileWork tile_work(const KParams& p, const TileGrid& tg, int t) {
+__device__ __forceinline__ TileWork tile_work(const KParams& p, const TileGrid& tg, int t, int spc = STAGES_PER_CHUNK) {
     int i, j;
     tg.locate(t, i, j);
     TileWork w;
@@ -73,7 +73,7 @@ __device__ __forceinline__ TileWork tile_work(const KParams& p, const TileGrid& 
     w.n0 = j * BN;
     w.kb = p.ktri ? (w.m0 / BK) * BK : 0;
     w.num_k = (p.K > w.kb) ? (p.K - w.kb + BK - 1) / BK : 0;
-    w.num_chunks = (w.num_k + STAGES_PER_CHUNK - 1) / STAGES_PER_CHUNK;   // 0 when there is nothing to multiply
+    w.num_chunks = (w.num_k + spc - 1) / spc;   // 0 when there is nothing to multiply
     return w;
 }
 
@@ -82,7 +82,12 @@ __device__ __forceinline__ TileWork tile_work(const KParams& p, const TileGrid& 
 // shared memory -- a ktri product has tiles of very different length, which a static assignment balances
 // badly.  The three roles keep their own running counters (stage ring position, accumulator-set use count),
 // so the drain of one tile's last K-chunk overlaps the MMAs of the next tile's first one.
-template <int EPI>
+// ACC: the accurate variant.  The tensor core truncates when it accumulates, so the error of a product grows with
+// the number of MMAs between two flushes of the accumulators (scripts/tc_accumulate_bias.py).  Here a flush happens
+// every 128 K-columns (16 MMAs) and goes into REGISTERS -- each epilogue thread keeps the 128 running sums of its
+// row, added in fp32 round-to-nearest -- so that C is read and written once per tile, as in the 512-column variant,
+// but with the accumulation error of 128-column products (profiles/r02/trsm_outer_block.md).
+template <int EPI, bool ACC = false>
 __global__ void __launch_bounds__(NTHREADS, 1)
 tgemm_tma_kernel(const KParams p, const TileGrid tg, int* __restrict__ tile_counter,
                  const __grid_constant__ CUtensorMap map_ah,
@@ -94,6 +99,7 @@ tgemm_tma_kernel(const KParams p, const TileGrid tg, int* __restrict__ tile_coun
     __shared__ int sched_tile[NSCHED];
     __shared__ uint32_t tmem_base_holder;
 
+    constexpr int SPC = ACC ? 128 / BK : STAGES_PER_CHUNK;      // stages between two flushes of the accumulators
     const int ntiles = tg.count();
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     // aligned by offset so that the pointer keeps its shared address space (LDS / STS instead of generic LD / ST)
@@ -141,7 +147,7 @@ tgemm_tma_kernel(const KParams p, const TileGrid tg, int* __restrict__ tile_coun
                 *reinterpret_cast<volatile int*>(&sched_tile[slot]) = t;
                 mbar_arrive(&sched_full[slot]);
                 if (t >= ntiles) break;
-                const TileWork w = tile_work(p, tg, t);
+                const TileWork w = tile_work(p, tg, t, SPC);
                 for (int kt = 0; kt < w.num_k; ++kt, ++it) {
                     const uint32_t s = it % NSTAGE;
                     if (it >= NSTAGE) mbar_wait(&empty_bar[s], (it / NSTAGE - 1) & 1);
@@ -166,13 +172,13 @@ tgemm_tma_kernel(const KParams p, const TileGrid tg, int* __restrict__ tile_coun
                 const int t = *reinterpret_cast<volatile int*>(&sched_tile[slot]);
                 mbar_arrive(&sched_empty[slot]);
                 if (t >= ntiles) break;
-                const TileWork w = tile_work(p, tg, t);
+                const TileWork w = tile_work(p, tg, t, SPC);
                 for (int chunk = 0; chunk < w.num_chunks; ++chunk, ++gc) {
                     const uint32_t set = gc & 1;
                     if (gc >= 2) mbar_wait(&acc_empty[set], (gc / 2 - 1) & 1);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     const uint32_t acc_hi = tmem_d + set * 256u, acc_x = acc_hi + 128u;
-                    const int kt_beg = chunk * STAGES_PER_CHUNK, kt_end = min(w.num_k, kt_beg + STAGES_PER_CHUNK);
+                    const int kt_beg = chunk * SPC, kt_end = min(w.num_k, kt_beg + SPC);
                     for (int kt = kt_beg; kt < kt_end; ++kt, ++it) {
                         const uint32_t s = it % NSTAGE;
                         mbar_wait(&full_bar[s], (it / NSTAGE) & 1);
@@ -211,7 +217,41 @@ tgemm_tma_kernel(const KParams p, const TileGrid tg, int* __restrict__ tile_coun
             const int t = *reinterpret_cast<volatile int*>(&sched_tile[slot]);
             mbar_arrive(&sched_empty[slot]);
             if (t >= ntiles) break;
-            const TileWork w = tile_work(p, tg, t);
+            const TileWork w = tile_work(p, tg, t, SPC);
+            if constexpr (ACC) {
+                float run[BN];                        // this row's running sums, one per column of the tile
+#pragma unroll
+                for (int c = 0; c < BN; ++c) run[c] = 0.f;
+                for (int chunk = 0; chunk < w.num_chunks; ++chunk, ++gc) {
+                    const uint32_t set = gc & 1;
+                    mbar_wait(&acc_full[set], (gc / 2) & 1);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+                    for (int c0 = 0; c0 < BN; c0 += 32) {
+                        uint32_t v[32], x[32];
+                        const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + set * 256u + (uint32_t)c0;
+                        tc::tmem_ld_32x32b_x32(v, taddr);
+                        tc::tmem_ld_32x32b_x32(x, taddr + 128u);
+                        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) run[c0 + i] += __uint_as_float(v[i]) + __uint_as_float(x[i]);
+                    }
+                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                    mbar_arrive(&acc_empty[set]);
+                }
+                // one pass over C: stage 32 columns at a time (this thread's row of the warp's 32 x 32 block)
+#pragma unroll
+                for (int c0 = 0; c0 < BN; c0 += 32) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        *reinterpret_cast<float4*>(tile + lane * EPI_LD + 4 * i) =
+                            make_float4(run[c0 + 4 * i], run[c0 + 4 * i + 1], run[c0 + 4 * i + 2], run[c0 + 4 * i + 3]);
+                    __syncwarp();
+                    epilogue_rows<EPI>(p, tile, alpha, p.beta, r1c, true, w.m0, w.n0, q, c0, lane);
+                    __syncwarp();
+                }
+                continue;
+            }
             const int passes = w.num_chunks > 0 ? w.num_chunks : 1;   // an empty product still applies beta / bias
             for (int chunk = 0; chunk < passes; ++chunk) {
                 const bool have_acc = w.num_chunks > 0;
@@ -343,18 +383,23 @@ int tma_split_operand(const float* x, int64_t ldx, int64_t rows, int64_t K, floa
 
 // C (M x N) = alpha A B^T (+ ...) from pre-split operands: a_* (M x K), b_* (N x K), leading dimension ceil4(K).
 int launch_gemm_tma_presplit(const KParams& p, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo,
-                             int* tile_counter, cudaStream_t stream) {
+                             int* tile_counter, cudaStream_t stream, int64_t ld_a, int64_t ld_b, bool accurate) {
     const int64_t M = p.M, N = p.N, K = p.K;
     const int64_t ldk = (K + 3) / 4 * 4;
+    if (ld_a <= 0) ld_a = ldk;
+    if (ld_b <= 0) ld_b = ldk;
+    PB_REQUIRE(ld_a % 4 == 0 && ld_b % 4 == 0 && ld_a >= ldk && ld_b >= ldk && aligned16(a_hi) && aligned16(a_lo) && aligned16(b_hi) &&
+                   aligned16(b_lo),
+               "gemm (TMA): pre-split operands must be 16-byte aligned with leading dimensions that are multiples of 4");
     PB_REQUIRE(p.vecC && p.ldc % 4 == 0 && aligned16(p.C), "gemm (TMA): C must be 16-byte aligned with ldc % 4 == 0");
     PB_REQUIRE(p.splitk == 1 && !p.post_wdiag, "gemm (TMA): split-K / look-ahead are not supported on this path");
     PB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm (TMA): empty product");
     alignas(64) CUtensorMap mah, mal, mbh, mbl;
     int rc;
-    if ((rc = make_map_box(&mah, a_hi, M, K, ldk))) return rc;
-    if ((rc = make_map_box(&mal, a_lo, M, K, ldk))) return rc;
-    if ((rc = make_map_box(&mbh, b_hi, N, K, ldk))) return rc;
-    if ((rc = make_map_box(&mbl, b_lo, N, K, ldk))) return rc;
+    if ((rc = make_map_box(&mah, a_hi, M, K, ld_a))) return rc;
+    if ((rc = make_map_box(&mal, a_lo, M, K, ld_a))) return rc;
+    if ((rc = make_map_box(&mbh, b_hi, N, K, ld_b))) return rc;
+    if ((rc = make_map_box(&mbl, b_lo, N, K, ld_b))) return rc;
     TileGrid tg;
     tg.gm = (int)ceil_div(M, BM); tg.gn = (int)ceil_div(N, BN); tg.lower = p.lower;
     const int ntiles = tg.count();
@@ -366,6 +411,10 @@ int launch_gemm_tma_presplit(const KParams& p, const float* a_hi, const float* a
         kern<<<grid, NTHREADS, SMEM_BYTES, stream>>>(p, tg, tile_counter, mah, mal, mbh, mbl);
         return check_launch("gemm (tcgen05 + TMA)");
     };
+    if (accurate) {
+        PB_REQUIRE(!p.r1u && !p.mirror && !p.act && !p.ktri, "gemm (TMA): the accurate variant is the plain alpha / beta product");
+        return launch(tgemm_tma_kernel<0, true>);
+    }
     if (p.r1u || p.mirror) return launch(tgemm_tma_kernel<2>);
     if (p.act) return launch(tgemm_tma_kernel<1>);
     return launch(tgemm_tma_kernel<0>);

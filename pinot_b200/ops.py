@@ -401,7 +401,14 @@ class ExactGPPosterior:
         g = gram_raw(self.kind, x_te, self.x_tr, self.scale, self.variance)
         if row_offset < n:   # _perturb of the rectangular K_te,tr: eps on its GLOBAL main diagonal (:95)
             g.diagonal(offset=int(row_offset)).add_(EPSILON)
-        call("trsm_rlt", ptr(self.l), self.ld, n, ptr(g), n, g.shape[0])
+        nbytes = _lib.trsm_rlt_workspace_bytes(n, g.shape[0])
+        if nbytes and n % 4 == 0:
+            # (one buffer per posterior, grown on demand: the split of L into it is repeated per call, 40 us at n = 4096)
+            if getattr(self, "_trsm_ws", None) is None or self._trsm_ws.numel() * 4 < nbytes:
+                self._trsm_ws = torch.empty((nbytes + 3) // 4, device=g.device, dtype=torch.float32)
+            call("trsm_rlt_ws", ptr(self.l), self.ld, n, ptr(g), n, g.shape[0], ptr(self._trsm_ws), nbytes)
+        else:
+            call("trsm_rlt", ptr(self.l), self.ld, n, ptr(g), n, g.shape[0])
         return g
 
     @torch.no_grad()

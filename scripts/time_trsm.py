@@ -20,3 +20,19 @@ for r in [int(v) for v in sys.argv[1:]] or (4096, 32768):
         ts = sorted(s.elapsed_time(e) for s, e in evs[1:])
         ms = ts[len(ts) // 2]
         print(json.dumps({"r": r, "n": n, "outer_block": int(ob), "ms": ms, "tflops_fp32_equiv": r * n * n / ms / 1e9}))
+    # the entry point with caller scratch: 512-column blocks, wide updates accumulated accurately on the TMA-fed GEMM
+    os.environ["PINOT_B200_TRSM_OB"] = "128"
+    from pinot_b200 import _lib
+    nbytes = _lib.trsm_rlt_workspace_bytes(n, r)
+    if nbytes:
+        ws = torch.empty(nbytes // 4, device=DEV)
+        x = x0.clone()
+        evs = []
+        for _ in range(5):
+            x.copy_(x0)
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record(); call("trsm_rlt_ws", ptr(l), n, n, ptr(x), n, r, ptr(ws), nbytes); e.record(); evs.append((s, e))
+        torch.cuda.synchronize()
+        ts = sorted(s.elapsed_time(e) for s, e in evs[1:])
+        ms = ts[len(ts) // 2]
+        print(json.dumps({"r": r, "n": n, "entry": "trsm_rlt_ws", "ms": ms, "tflops_fp32_equiv": r * n * n / ms / 1e9}))

@@ -559,6 +559,31 @@ def test_trsm_rlt(n, r):
     assert rel_err(xd, want) < 1e-4
 
 
+@pytest.mark.parametrize("n,r", [(1024, 1500), (1792, 1100), (2400, 1024)])
+def test_trsm_rlt_with_workspace_matches_the_plain_solve(n, r):
+    """pinot_b200_trsm_rlt_ws: the wide updates on the TMA-fed GEMM with accumulators flushed into registers every
+    128 K-columns.  Against the fp64 solve, and against the plain schedule on the same inputs (both 128-wide
+    accumulation: they agree to fp32 rounding); ragged last block (n = 1792 = 3.5 x 512, n = 2400)."""
+    from pinot_b200 import _lib
+    l = torch.linalg.cholesky(_spd(n, n + 1))
+    b = torch.randn(r, n, dtype=torch.float64)
+    ld = l.float().to(DEV).contiguous()
+    x1, x2 = b.float().to(DEV).contiguous(), b.float().to(DEV).contiguous()
+    nbytes = _lib.trsm_rlt_workspace_bytes(n, r)
+    assert nbytes > 0
+    ws = torch.empty(nbytes // 4, device=DEV)
+    pb._lib.call("trsm_rlt_ws", ld.data_ptr(), n, n, x1.data_ptr(), n, r, ws.data_ptr(), nbytes)
+    pb._lib.call("trsm_rlt", ld.data_ptr(), n, n, x2.data_ptr(), n, r)
+    want = torch.linalg.solve_triangular(l, b.t(), upper=False).t()
+    assert rel_err(x1, want) < 1e-4 and rel_err(x2, want) < 1e-4
+    assert rel_err(x1, x2) < 2e-6
+    # no workspace / too small a problem: the plain schedule, same answer
+    x3 = b.float().to(DEV).contiguous()
+    pb._lib.call("trsm_rlt_ws", ld.data_ptr(), n, n, x3.data_ptr(), n, r, None, 0)
+    assert torch.equal(x3, x2)
+    assert _lib.trsm_rlt_workspace_bytes(512, 4096) == 0
+
+
 @pytest.mark.parametrize("n,r", [(90, 4), (200, 33)])
 def test_chol_solve_autograd(n, r):
     torch.manual_seed(n)
