@@ -15,7 +15,8 @@ changes nothing); otherwise the entry keeps its dense features and is shipped as
 ``PackedDataset`` mirrors the reference class where its behaviour decides what a training loop sees:
 ``len`` counts molecules (datasets.py:25-31), integer / slice indexing (:33-42), iteration (:44-49), ``shuffle``
 reseeds Python's ``random`` and shuffles in place (:64-69), ``split`` = shuffle + ``utils.split`` (:51-62),
-``batch`` (:71-74), ``+`` (:105-108), ``to`` (:110-113)."""
+``batch`` (:71-74), ``save`` / ``load`` (:76-103, one file holding the packed arrays), ``+`` (:105-108), ``to``
+(:110-113)."""
 import random
 
 import torch
@@ -176,6 +177,26 @@ class PackedDataset:
 
     def transfer_bytes(self):
         return sum(e.transfer_bytes() for e in self.ds)
+
+    # ---- on-disk form (the reference's Dataset.save / load, datasets.py:76-103, go through dgl.save_graphs) ---------
+    def save(self, path):
+        """Write the entries as they are held -- compact features, edge lists, counts, targets -- to one file."""
+        torch.save({"format": "pinot_b200.PackedDataset/1",
+                    "entries": [{"src": e.src, "dst": e.dst, "num_nodes": e.num_nodes, "batch_num_nodes": e.batch_num_nodes,
+                                 "batch_num_edges": e.batch_num_edges, "y": e.y, "z": e.z, "fp": e.fp, "h": e.h,
+                                 "n_onehot": e.n_onehot} for e in (self.ds or [])]}, path)
+
+    def load(self, path, indices=None):
+        """Read a file written by :meth:`save` (``indices``: a subset of its entries, as in the reference)."""
+        blob = torch.load(path, map_location="cpu", weights_only=False)
+        if blob.get("format") != "pinot_b200.PackedDataset/1":
+            raise ValueError("not a PackedDataset file: %r" % (path,))
+        entries = blob["entries"]
+        if indices is not None:
+            entries = [entries[i] for i in indices]
+        self.ds = [PackedBatch(d["src"], d["dst"], d["num_nodes"], d["batch_num_nodes"], d["batch_num_edges"], d["y"],
+                               z=d["z"], fp=d["fp"], h=d["h"], n_onehot=d["n_onehot"]) for d in entries]
+        return self
 
     def to(self, device):
         """Device-resident ``(graph, y)`` entries (a plain list: what a training loop iterates over)."""

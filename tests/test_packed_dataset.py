@@ -170,3 +170,19 @@ def test_packed_entry_on_the_device_equals_the_dense_upload():
     assert torch.equal(g2.ndata["h"], ref.ndata["h"]) and torch.equal(y2.cpu(), y)
     assert up.h2d_bytes < 0.25 * (g.ndata["h"].numel() * 4)
     up.release()
+
+
+def test_save_and_load_round_trip(tmp_path):
+    ds = PackedDataset.from_pairs(_pairs(4, 5, seed=30))
+    path = str(tmp_path / "pool.pt")
+    ds.save(path)
+    back = PackedDataset().load(path)
+    assert len(back) == len(ds) == 20 and len(back.ds) == 4
+    for a, b in zip(ds.ds, back.ds):
+        assert a.compact == b.compact and torch.equal(a.features(), b.features()) and torch.equal(a.y, b.y)
+        assert torch.equal(a.src, b.src) and torch.equal(a.dst, b.dst) and a.batch_num_nodes == b.batch_num_nodes
+    sub = PackedDataset().load(path, indices=[2, 0])
+    assert len(sub.ds) == 2 and torch.equal(sub.ds[0].y, ds.ds[2].y)
+    with pytest.raises(ValueError):
+        torch.save({"format": "something else"}, path)
+        PackedDataset().load(path)
