@@ -84,14 +84,26 @@ __device__ __forceinline__ int factor_diag_block_regs(const float* src, int64_t 
         const float inv = rsqrtf(d);
         const float y = a[j] * inv * inv;          // S[r][j] / d
         a[j] *= inv;                               // L[r][j] (row j: sqrt(d)), or M[r][j]
-        // S[r][c] -= S[r][j] S[c][j] / d for c > j; column read in aligned 16-byte pieces
+        // S[r][c] -= S[r][j] S[c][j] / d for c > j; column read in aligned 16-byte pieces.  Pairs of columns go
+        // through the packed FFMA2 (fma.rn.f32x2, same rounding as two FFMAs): this code is unrolled 64-fold and runs
+        // once per call, at the pace of the instruction fetch path (scripts/micro/factor_time.cu) -- half the FMA
+        // instructions is half of most of its bytes.
+        const float2 ny2 = make_float2(-y, -y);
 #pragma unroll
         for (int c4 = ((j + 1) / 4) * 4; c4 < DIAG_NB; c4 += 4) {
             const float4 l = *reinterpret_cast<const float4*>(Lt + j * DIAG_LT + c4);
-            if (c4 + 0 > j) a[c4 + 0] = fmaf(-y, l.x, a[c4 + 0]);
-            if (c4 + 1 > j) a[c4 + 1] = fmaf(-y, l.y, a[c4 + 1]);
-            if (c4 + 2 > j) a[c4 + 2] = fmaf(-y, l.z, a[c4 + 2]);
-            if (c4 + 3 > j) a[c4 + 3] = fmaf(-y, l.w, a[c4 + 3]);
+            if (c4 + 0 > j) {
+                const float2 t = __ffma2_rn(ny2, make_float2(l.x, l.y), make_float2(a[c4 + 0], a[c4 + 1]));
+                a[c4 + 0] = t.x; a[c4 + 1] = t.y;
+            } else if (c4 + 1 > j) {
+                a[c4 + 1] = fmaf(-y, l.y, a[c4 + 1]);
+            }
+            if (c4 + 2 > j) {
+                const float2 t = __ffma2_rn(ny2, make_float2(l.z, l.w), make_float2(a[c4 + 2], a[c4 + 3]));
+                a[c4 + 2] = t.x; a[c4 + 3] = t.y;
+            } else if (c4 + 3 > j) {
+                a[c4 + 3] = fmaf(-y, l.w, a[c4 + 3]);
+            }
         }
     }
     // results: thread r < 64 holds row r of L11 (entries c <= r), thread 64 + r row r of M (c >= r)
