@@ -81,7 +81,8 @@ __device__ __forceinline__ int factor_diag_block_regs(const float* src, int64_t 
             if (fail < 0 && j < nb) fail = j;
             d = 1.f;
         }
-        const float inv = rsqrtf(d);
+        float inv;                                 // MUFU.RSQ alone: rsqrtf() wraps it in a denormal rescue (a pivot is
+        asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(d));   // never denormal; same value for normal inputs)
         const float y = a[j] * inv * inv;          // S[r][j] / d
         a[j] *= inv;                               // L[r][j] (row j: sqrt(d)), or M[r][j]
         // S[r][c] -= S[r][j] S[c][j] / d for c > j; column read in aligned 16-byte pieces.  Pairs of columns go
