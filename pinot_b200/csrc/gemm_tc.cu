@@ -477,19 +477,23 @@ __global__ void __launch_bounds__(NTHREADS, BN == 128 ? 2 : 1) tgemm_kernel(cons
             PB_STAMP(6);
         }
         if (p.post_solve) {
-            if (!owner) wait_flag(p.post_flag);
-            else __syncthreads();
-            if (POST && p.post_solve == 2) {
-                // ---- panel solve X <- X M on the tensor cores (nb == 64, 16-byte aligned rows) ----
-                // operands: A = this tile's 128 rows of the panel (K = 64), B = M^T (N = 64), both split to
-                // hi / lo over the whole K in the idle pipeline memory; 24 MMAs; the result goes back in place.
-                constexpr int LBOB = G::SOLVE_LBO_B;
-                uint8_t* x_hi = smem;
-                uint8_t* x_lo = smem + G::SOLVE_A;
-                uint8_t* m_hi = smem + 2 * G::SOLVE_A;
-                uint8_t* m_lo = m_hi + G::SOLVE_B;
-                {
-                    float4 xr[8], mr[4];
+            const bool tc = POST && p.post_solve == 2;
+            // The rows of the panel this tile solves are its own epilogue's output: a tile that has to wait for the
+            // factor (every tile of column 0 but the owner) loads, splits and stages them BEFORE it waits, so that
+            // only M is on the path after the flag.  (One copy of the staging code: a two-pass loop.)
+            constexpr int LBOB = G::SOLVE_LBO_B;
+            uint8_t* x_hi = smem;
+            uint8_t* x_lo = smem + G::SOLVE_A;
+            uint8_t* m_hi = smem + 2 * G::SOLVE_A;
+            uint8_t* m_lo = m_hi + G::SOLVE_B;
+#pragma unroll 1
+            for (int pass = 0; pass < 2; ++pass) {
+                if (pass == 1) {
+                    if (!owner) wait_flag(p.post_flag);
+                    else __syncthreads();
+                }
+                if (tc && (pass == 0) == !owner) {
+                    float4 xr[8];
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {          // all loads first: one L2 round trip
                         const int idx = tid + i * 256;
@@ -498,13 +502,6 @@ __global__ void __launch_bounds__(NTHREADS, BN == 128 ? 2 : 1) tgemm_kernel(cons
                         xr[i] = make_float4(0.f, 0.f, 0.f, 0.f);
                         if (m >= p.post_nb && m < p.M)
                             xr[i] = __ldcg(reinterpret_cast<const float4*>(p.C + (int64_t)m * p.ldc + kc * 4));
-                    }
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const int idx = tid + i * 256;
-                        const int n = idx & 63, kc = idx >> 6;     // B[n][k] = M[k][n]
-                        const float* src = p.post_winv + (kc * 4) * DIAG_NB + n;
-                        mr[i] = make_float4(__ldcg(src), __ldcg(src + DIAG_NB), __ldcg(src + 2 * DIAG_NB), __ldcg(src + 3 * DIAG_NB));
                     }
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
@@ -516,6 +513,21 @@ __global__ void __launch_bounds__(NTHREADS, BN == 128 ? 2 : 1) tgemm_kernel(cons
                         const int off = kc * G::LBO_A + row * 16;
                         *reinterpret_cast<float4*>(x_hi + off) = h;
                         *reinterpret_cast<float4*>(x_lo + off) = l;
+                    }
+                }
+            }
+            if (tc) {
+                // ---- panel solve X <- X M on the tensor cores (nb == 64, 16-byte aligned rows) ----
+                // operands: A = this tile's 128 rows of the panel (K = 64, staged above), B = M^T (N = 64), both split
+                // to hi / lo over the whole K in the idle pipeline memory; 24 MMAs; the result goes back in place.
+                {
+                    float4 mr[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int idx = tid + i * 256;
+                        const int n = idx & 63, kc = idx >> 6;     // B[n][k] = M[k][n]
+                        const float* src = p.post_winv + (kc * 4) * DIAG_NB + n;
+                        mr[i] = make_float4(__ldcg(src), __ldcg(src + DIAG_NB), __ldcg(src + 2 * DIAG_NB), __ldcg(src + 3 * DIAG_NB));
                     }
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
