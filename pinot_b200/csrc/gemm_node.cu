@@ -10,8 +10,9 @@
 //               to the producer at once;
 //   warp 1      MMA issuer: 3 tcgen05.mma per k-step (lo.hi + hi.lo -> cross accumulator, hi.hi -> main one)
 //               against the resident pre-split B, tcgen05.commit frees the operand buffer;
-//   warps 2-9   epilogue: tcgen05.ld (thread = output row, 32 consecutive columns), bias / tanh / beta, 32-byte
-//               stores (st.global.v8: whole L2 sectors) straight from that layout; two warps per TMEM lane quadrant;
+//   warps 2-9   epilogue: the product is accumulated TRANSPOSED (weights on the M side), so tcgen05.ld gives each
+//               thread one output column and 32 consecutive rows; bias / tanh / beta, then one 4-byte store per row:
+//               a warp's request is 128 contiguous bytes of one row (one L1 wavefront); two warps per lane quadrant;
 // accumulators double-buffered in TMEM so that the epilogue of row tile t overlaps the MMAs of tile t + 1.
 #include "gemm_params.cuh"
 #include "gemm_epilogue.cuh"
@@ -49,7 +50,7 @@ __device__ __forceinline__ void split4(const float4 v, float4& h, float4& l) {
 
 template <int EPI>
 __global__ void __launch_bounds__(NTHREADS, 1)
-node_gemm_kernel(const KParams p, const int transB, const __grid_constant__ CUtensorMap map_a) {
+node_gemm_kernel(const KParams p, const int transB, const __grid_constant__ CUtensorMap map_a, const int l2_ahead) {
     extern __shared__ __align__(1024) uint8_t dyn_smem[];
     __shared__ __align__(8) uint64_t raw_full[NRAW], raw_empty[NRAW], op_full[NOP], op_empty[NOP], acc_full[2], acc_empty[2];
     __shared__ uint32_t tmem_base_holder;
@@ -139,14 +140,25 @@ node_gemm_kernel(const KParams p, const int transB, const __grid_constant__ CUte
                     if (it >= NRAW) mbar_wait(&raw_empty[s], (it / NRAW - 1) & 1);
                     mbar_expect_tx(&raw_full[s], SLAB_BYTES);
                     tma_load_2d(raw_ring + s * SLAB_BYTES, &map_a, ks * BK, t * BM, &raw_full[s]);
+                    // Two 16 KB landing slots are too few bytes in flight to cover the HBM latency; the same slab of
+                    // this CTA's NEXT row tile is pulled into L2 now, so that its TMA load later is an L2 hit.
+                    if (l2_ahead && t + (int)gridDim.x < ntiles)
+                        asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(&map_a),
+                                     "r"(ks * BK), "r"((t + (int)gridDim.x) * BM)
+                                     : "memory");
                 }
             }
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
         if (lane == 0) {
-            const int n_mma = min(128, ((p.N + 15) / 16) * 16);
-            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n_mma >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+            // The product is accumulated TRANSPOSED: the weight slabs are the M-side operand (output column = TMEM lane,
+            // zero rows beyond p.N) and the row slab is the N-side one (row of the tile = TMEM column).  Both are
+            // 128-row K-major SWIZZLE_128B slabs, so only the descriptors trade places.  The epilogue then holds one
+            // output COLUMN per thread and a warp's store covers 32 consecutive floats of one row: one 128-byte
+            // wavefront per request instead of ~46 (thread = row: 32 rows x 32 bytes), which had the LSU data path
+            // at 83 % (profiles/r02/node_gemm_data_pipe.md).
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BM >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
             uint32_t it = 0, gc = 0;
             for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++gc) {
                 const uint32_t set = gc & 1;
@@ -164,9 +176,9 @@ node_gemm_kernel(const KParams p, const int transB, const __grid_constant__ CUte
                     for (int k8 = 0; k8 < BK / 8; ++k8) {
                         const uint64_t adv = (uint64_t)((k8 * 32) >> 4);
                         const uint32_t acc = (ks > 0 || k8 > 0) ? 1u : 0u;
-                        mma_tf32(acc_x, d_al + adv, d_bh + adv, idesc, acc);
-                        mma_tf32(acc_x, d_ah + adv, d_bl + adv, idesc, 1u);
-                        mma_tf32(acc_hi, d_ah + adv, d_bh + adv, idesc, acc);
+                        mma_tf32(acc_x, d_bh + adv, d_al + adv, idesc, acc);
+                        mma_tf32(acc_x, d_bl + adv, d_ah + adv, idesc, 1u);
+                        mma_tf32(acc_hi, d_bh + adv, d_ah + adv, idesc, acc);
                     }
                     mma_commit(&op_empty[o]);
                 }
@@ -175,6 +187,8 @@ node_gemm_kernel(const KParams p, const int transB, const __grid_constant__ CUte
         }
     } else if (warp >= CONV_WARP0) {
         // ===================== converters =====================
+        // (A second converter group on alternate slabs was measured: +3 % before the transposed accumulator, nothing
+        //  after it, and its 576 threads cap the epilogue at 96 registers.)
         const int ct = tid - CONV_WARP0 * 32;      // 0 .. 127
         uint32_t it = 0;
         for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
@@ -207,69 +221,45 @@ node_gemm_kernel(const KParams p, const int transB, const __grid_constant__ CUte
         }
     } else {
         // ===================== epilogue warps (2..9) =====================
+        // thread = output column n (TMEM lane), registers = 32 consecutive rows of the tile
         const float alpha = p.alpha, beta = p.beta;
-        const int q = warp & 3;                 // TMEM lane quadrant of this warp
-        const int half = (warp - 2) >> 2;       // which column blocks: half 0 -> 0, 64; half 1 -> 32, 96
-        const bool wide_st = (p.ldc % 8 == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 31) == 0);
+        const int q = warp & 3;                 // TMEM lane quadrant of this warp: columns 32 q .. 32 q + 31
+        const int half = (warp - 2) >> 2;       // which row blocks: half 0 -> 0, 64; half 1 -> 32, 96
+        const int n = q * 32 + lane;
+        const bool n_ok = n < p.N;
+        const float bias = (p.bias && n_ok) ? __ldg(p.bias + n) : 0.f;
         uint32_t gc = 0;
         for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++gc) {
             const uint32_t set = gc & 1;
             mbar_wait(&acc_full[set], (gc / 2) & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const int m = t * BM + q * 32 + lane;
 #pragma unroll 1
-            for (int c0 = half * 32; c0 < p.N; c0 += 64) {
+            for (int r0 = half * 32; r0 < BM; r0 += 64) {
+                const int rows_left = p.M - (t * BM + r0);
+                if (rows_left <= 0 || q * 32 >= p.N) break;        // warp-uniform
                 uint32_t v[32], x[32];
-                const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + set * 256u + (uint32_t)c0;
-                asm volatile(
-                    "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-                    "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-                    "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
-                    : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                      "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
-                      "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
-                      "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-                    : "r"(taddr)
-                    : "memory");
-                asm volatile(
-                    "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-                    "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-                    "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
-                    : "=r"(x[0]), "=r"(x[1]), "=r"(x[2]), "=r"(x[3]), "=r"(x[4]), "=r"(x[5]), "=r"(x[6]), "=r"(x[7]),
-                      "=r"(x[8]), "=r"(x[9]), "=r"(x[10]), "=r"(x[11]), "=r"(x[12]), "=r"(x[13]), "=r"(x[14]), "=r"(x[15]),
-                      "=r"(x[16]), "=r"(x[17]), "=r"(x[18]), "=r"(x[19]), "=r"(x[20]), "=r"(x[21]), "=r"(x[22]), "=r"(x[23]),
-                      "=r"(x[24]), "=r"(x[25]), "=r"(x[26]), "=r"(x[27]), "=r"(x[28]), "=r"(x[29]), "=r"(x[30]), "=r"(x[31])
-                    : "r"(taddr + 128u)
-                    : "memory");
+                const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + set * 256u + (uint32_t)r0;
+                tmem_ld_32x32b_x32(v, taddr);
+                tmem_ld_32x32b_x32(x, taddr + 128u);
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                if (m < p.M) {
-                    float* crow = p.C + (int64_t)m * p.ldc;
+                if (n_ok) {
+                    float* cp = p.C + (int64_t)(t * BM + r0) * p.ldc + n;
                     // same arithmetic order as epilogue_rows: alpha * acc + (beta * c + bias)
-                    auto finish = [&](int i, int n) -> float4 {
-                        float4 c = make_float4(0.f, 0.f, 0.f, 0.f), b = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (beta != 0.f) c = *reinterpret_cast<const float4*>(crow + n);
-                        if (p.bias) b = __ldg(reinterpret_cast<const float4*>(p.bias + n));
-                        float4 o;
-                        o.x = fmaf(alpha, __uint_as_float(v[4 * i + 0]) + __uint_as_float(x[4 * i + 0]), fmaf(beta, c.x, b.x));
-                        o.y = fmaf(alpha, __uint_as_float(v[4 * i + 1]) + __uint_as_float(x[4 * i + 1]), fmaf(beta, c.y, b.y));
-                        o.z = fmaf(alpha, __uint_as_float(v[4 * i + 2]) + __uint_as_float(x[4 * i + 2]), fmaf(beta, c.z, b.z));
-                        o.w = fmaf(alpha, __uint_as_float(v[4 * i + 3]) + __uint_as_float(x[4 * i + 3]), fmaf(beta, c.w, b.w));
-                        if (EPI == 1) { o.x = tanhf(o.x); o.y = tanhf(o.y); o.z = tanhf(o.z); o.w = tanhf(o.w); }
-                        return o;
-                    };
 #pragma unroll
-                    for (int i = 0; i < 8; i += 2) {
-                        const int n = c0 + 4 * i;     // N % 4 == 0 (node_gemm_applicable): whole 16-byte groups only
-                        if (wide_st && n + 8 <= p.N) {
-                            // one 32-byte store per pair of groups: whole L2 sectors instead of half ones
-                            const float4 o0 = finish(i, n), o1 = finish(i + 1, n + 4);
-                            asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(crow + n), "f"(o0.x),
-                                         "f"(o0.y), "f"(o0.z), "f"(o0.w), "f"(o1.x), "f"(o1.y), "f"(o1.z), "f"(o1.w)
-                                         : "memory");
-                        } else {
-                            if (n < p.N) *reinterpret_cast<float4*>(crow + n) = finish(i, n);
-                            if (n + 4 < p.N) *reinterpret_cast<float4*>(crow + n + 4) = finish(i + 1, n + 4);
+                    for (int i0 = 0; i0 < 32; i0 += 8) {
+                        float c[8], o[8];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) c[i] = (beta != 0.f && i0 + i < rows_left) ? cp[(int64_t)(i0 + i) * p.ldc] : 0.f;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i)
+                            o[i] = fmaf(alpha, __uint_as_float(v[i0 + i]) + __uint_as_float(x[i0 + i]), fmaf(beta, c[i], bias));
+                        if (EPI == 1) {
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) o[i] = tanhf(o[i]);
                         }
+#pragma unroll
+                        for (int i = 0; i < 8; ++i)
+                            if (i0 + i < rows_left) cp[(int64_t)(i0 + i) * p.ldc] = o[i];
                     }
                 }
             }
@@ -315,9 +305,11 @@ int launch_node_gemm(const GemmParams& g, cudaStream_t stream) {
     const int ntiles = (int)ceil_div(g.M, BM);
     const unsigned grid = (unsigned)(ntiles < num_sms() ? ntiles : num_sms());
     const int transB = g.transB ? 1 : 0;
+    const char* e = getenv("PINOT_B200_NODE_L2_AHEAD");
+    const int l2_ahead = e ? (e[0] != '0') : 1;
     auto launch = [&](auto kern) -> int {
         PB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        kern<<<grid, NTHREADS, SMEM_BYTES, stream>>>(p, transB, map_a);
+        kern<<<grid, NTHREADS, SMEM_BYTES, stream>>>(p, transB, map_a, l2_ahead);
         return check_launch("node gemm (tcgen05 + TMA)");
     };
     if (g.act) return launch(node_gemm_kernel<1>);
