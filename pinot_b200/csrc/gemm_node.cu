@@ -5,14 +5,14 @@
 // Persistent CTA per SM, five roles, no thread ever waits on global memory latency:
 //   warp 0      TMA producer: raw fp32 slabs of A (128 rows x 32 columns, SWIZZLE_128B) into a 2-slot landing ring
 //               (B leaves room for no more; a slot is handed back as soon as it has been read, not when consumed);
-//   warps 10-13 converters: split a landed slab into tf32 hi / lo operand buffers -- the swizzled layout is
+//   warps 18-21 converters: split a landed slab into tf32 hi / lo operand buffers -- the swizzled layout is
 //               position-preserving, so the split is a flat 16-byte-chunk loop -- and hand the landing slot back
 //               to the producer at once;
 //   warp 1      MMA issuer: 3 tcgen05.mma per k-step (lo.hi + hi.lo -> cross accumulator, hi.hi -> main one)
 //               against the resident pre-split B, tcgen05.commit frees the operand buffer;
-//   warps 2-9   epilogue: the product is accumulated TRANSPOSED (weights on the M side), so tcgen05.ld gives each
+//   warps 2-17  epilogue: the product is accumulated TRANSPOSED (weights on the M side), so tcgen05.ld gives each
 //               thread one output column and 32 consecutive rows; bias / tanh / beta, then one 4-byte store per row:
-//               a warp's request is 128 contiguous bytes of one row (one L1 wavefront); two warps per lane quadrant;
+//               a warp's request is 128 contiguous bytes of one row (one L1 wavefront); four warps per lane quadrant;
 // accumulators double-buffered in TMEM so that the epilogue of row tile t overlaps the MMAs of tile t + 1.
 #include "gemm_params.cuh"
 #include "gemm_epilogue.cuh"
@@ -33,8 +33,8 @@ constexpr int B_BYTES = 2 * MAX_SLABS * SLAB_BYTES; // hi | lo, 128 KB
 constexpr int RAW_BYTES = NRAW * SLAB_BYTES;        // 32 KB
 constexpr int OP_BYTES = NOP * 2 * SLAB_BYTES;      // per buffer: hi | lo
 constexpr int SMEM_BYTES = B_BYTES + RAW_BYTES + OP_BYTES;   // 224 KB (+ 1 KB static) of the 227 KB a CTA may have
-constexpr int NTHREADS = 448;                       // producer, MMA, 8 epilogue warps, 4 converter warps
-constexpr int EPI_WARPS = 8, CONV_WARP0 = 2 + EPI_WARPS;
+constexpr int NTHREADS = 704;                       // producer, MMA, 16 epilogue warps, 4 converter warps
+constexpr int EPI_WARPS = 16, CONV_WARP0 = 2 + EPI_WARPS;
 constexpr int BTASKS = (BM * MAX_SLABS * 8 + NTHREADS - 1) / NTHREADS;   // 16-byte chunks of B per thread
 
 __device__ __forceinline__ void split4(const float4 v, float4& h, float4& l) {
@@ -220,11 +220,14 @@ node_gemm_kernel(const KParams p, const int transB, const __grid_constant__ CUte
             }
         }
     } else {
-        // ===================== epilogue warps (2..9) =====================
-        // thread = output column n (TMEM lane), registers = 32 consecutive rows of the tile
+        // ===================== epilogue warps (2..17) =====================
+        // thread = output column n (TMEM lane), registers = consecutive rows of the tile.  Sixteen warps (one per lane
+        // quadrant and 32-row block): the tanh of a row block is a chain of dependent MUFU / FMA instructions that
+        // ptxas does not interleave across elements, and with eight warps the tanh variant ran at the pace of that
+        // chain (5.6 us per row tile against 3.8 without the activation).
         const float alpha = p.alpha, beta = p.beta;
         const int q = warp & 3;                 // TMEM lane quadrant of this warp: columns 32 q .. 32 q + 31
-        const int half = (warp - 2) >> 2;       // which row blocks: half 0 -> 0, 64; half 1 -> 32, 96
+        const int r0 = ((warp - 2) >> 2) * 32;  // its rows of the tile
         const int n = q * 32 + lane;
         const bool n_ok = n < p.N;
         const float bias = (p.bias && n_ok) ? __ldg(p.bias + n) : 0.f;
@@ -233,33 +236,35 @@ node_gemm_kernel(const KParams p, const int transB, const __grid_constant__ CUte
             const uint32_t set = gc & 1;
             mbar_wait(&acc_full[set], (gc / 2) & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const int rows_left = p.M - (t * BM + r0);
+            if (rows_left > 0 && q * 32 < p.N) {                  // warp-uniform
 #pragma unroll 1
-            for (int r0 = half * 32; r0 < BM; r0 += 64) {
-                const int rows_left = p.M - (t * BM + r0);
-                if (rows_left <= 0 || q * 32 >= p.N) break;        // warp-uniform
-                uint32_t v[32], x[32];
-                const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + set * 256u + (uint32_t)r0;
-                tmem_ld_32x32b_x32(v, taddr);
-                tmem_ld_32x32b_x32(x, taddr + 128u);
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                if (n_ok) {
-                    float* cp = p.C + (int64_t)(t * BM + r0) * p.ldc + n;
-                    // same arithmetic order as epilogue_rows: alpha * acc + (beta * c + bias)
+                for (int h0 = 0; h0 < 32; h0 += 16) {
+                    uint32_t v[16], x[16];
+                    const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + set * 256u + (uint32_t)(r0 + h0);
+                    tmem_ld_32x32b_x16(v, taddr);
+                    tmem_ld_32x32b_x16(x, taddr + 128u);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    if (n_ok) {
+                        float* cp = p.C + (int64_t)(t * BM + r0 + h0) * p.ldc + n;
+                        const int left = rows_left - h0;
+                        // same arithmetic order as epilogue_rows: alpha * acc + (beta * c + bias)
 #pragma unroll
-                    for (int i0 = 0; i0 < 32; i0 += 8) {
-                        float c[8], o[8];
+                        for (int i0 = 0; i0 < 16; i0 += 8) {
+                            float c[8], o[8];
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) c[i] = (beta != 0.f && i0 + i < rows_left) ? cp[(int64_t)(i0 + i) * p.ldc] : 0.f;
+                            for (int i = 0; i < 8; ++i) c[i] = (beta != 0.f && i0 + i < left) ? cp[(int64_t)(i0 + i) * p.ldc] : 0.f;
 #pragma unroll
-                        for (int i = 0; i < 8; ++i)
-                            o[i] = fmaf(alpha, __uint_as_float(v[i0 + i]) + __uint_as_float(x[i0 + i]), fmaf(beta, c[i], bias));
-                        if (EPI == 1) {
+                            for (int i = 0; i < 8; ++i)
+                                o[i] = fmaf(alpha, __uint_as_float(v[i0 + i]) + __uint_as_float(x[i0 + i]), fmaf(beta, c[i], bias));
+                            if (EPI == 1) {
 #pragma unroll
-                            for (int i = 0; i < 8; ++i) o[i] = tanhf(o[i]);
+                                for (int i = 0; i < 8; ++i) o[i] = tanhf(o[i]);
+                            }
+#pragma unroll
+                            for (int i = 0; i < 8; ++i)
+                                if (i0 + i < left) cp[(int64_t)(i0 + i) * p.ldc] = o[i];
                         }
-#pragma unroll
-                        for (int i = 0; i < 8; ++i)
-                            if (i0 + i < rows_left) cp[(int64_t)(i0 + i) * p.ldc] = o[i];
                     }
                 }
             }
