@@ -411,7 +411,7 @@ def measure_train_step(ctx, n_mol, steps, warmup, want_e2e, sample_clocks):
                 dst_t.copy_(src_t, non_blocking=True)
             s_d, d_d, y_d, b_d = dev_ts[:4]
             gs = BatchedGraph(s_d, d_d, packed.num_nodes, bnn, bne, validate=False, batch_num_nodes_device=b_d)
-            gs.ndata["h"] = ops.expand_atom_features(dev_ts[4], dev_ts[5], packed.n_onehot) if packed.compact else dev_ts[4]
+            gs.ndata["h"] = ops.expand_atom_features(dev_ts[4], dev_ts[5], packed.n_onehot, pad_pitch=True) if packed.compact else dev_ts[4]
             gs.csr()
             ev = torch.cuda.Event()
             ev.record(copy_stream)

@@ -141,7 +141,7 @@ class CapturedBatchUpload:
                 d.copy_(h, non_blocking=True)
             g = BatchedGraph(self.dev[0], self.dev[1], self.meta[0], self.meta[1], self.meta[2], validate=False,
                              batch_num_nodes_device=self.dev[3])
-            g.ndata["h"] = ops.expand_atom_features(self.dev[4], self.dev[5], n_onehot) if compact else self.dev[4]
+            g.ndata["h"] = ops.expand_atom_features(self.dev[4], self.dev[5], n_onehot, pad_pitch=True) if compact else self.dev[4]
             g.csr()
             return g
 

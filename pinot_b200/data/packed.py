@@ -118,7 +118,7 @@ class PackedBatch:
         y = self.y.to(device, non_blocking=non_blocking)
         if self.compact:
             h = ops.expand_atom_features(self.z.to(device, non_blocking=non_blocking),
-                                         self.fp.to(device, non_blocking=non_blocking), self.n_onehot)
+                                         self.fp.to(device, non_blocking=non_blocking), self.n_onehot, pad_pitch=True)
         else:
             h = self.h.to(device, non_blocking=non_blocking)
         g = _graph.BatchedGraph(src, dst, self.num_nodes, self.batch_num_nodes, self.batch_num_edges, validate=False)

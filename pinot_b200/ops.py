@@ -123,6 +123,14 @@ class _NodeUpdate(torch.autograd.Function):
 def node_update(x, w, b=None, y_prev=None, w_is_out_in=True, act=None):
     """``act(x W + b [+ y_prev])``; ``act`` is None or "tanh"."""
     assert act in (None, "tanh"), "fused activation must be None or 'tanh'"
+    base = getattr(x, "_pb_pitch_base", None)
+    if (base is not None and not x.requires_grad and x.dtype == torch.float32 and x.dim() == 2 and x.data_ptr() == base.data_ptr()
+            and base.shape[0] == x.shape[0] and x.stride() == (base.shape[1], 1)):
+        # x is the (n, F) view of a zero-padded (n, pad4(F)) buffer (expand_atom_features(pad_pitch=True)): multiply the
+        # whole buffer by the weight with zero rows appended -- the same sum, on 16-byte aligned rows
+        pad = base.shape[1] - x.shape[1]
+        w = torch.nn.functional.pad(w, (0, pad) if w_is_out_in else (0, 0, 0, pad))
+        x = base
     return _NodeUpdate.apply(x, w, b, y_prev, bool(w_is_out_in), 1 if act == "tanh" else 0)
 
 
@@ -511,14 +519,26 @@ def chol_solve(k, b, check=True, info_sink=None):
     return _CholSolve.apply(k, b, check, info_sink)
 
 
-def expand_atom_features(z, fp, n_onehot=100):
+def expand_atom_features(z, fp, n_onehot=100, pad_pitch=False):
     """Dense ``(n_atoms, n_onehot + n_fp)`` fp32 atom features from their compact form (uint8 atomic number,
-    fp16 or fp32 fingerprint columns): what pinot/graph.py:163-173 builds per atom on the host."""
+    fp16 or fp32 fingerprint columns): what pinot/graph.py:163-173 builds per atom on the host.
+
+    ``pad_pitch``: lay the rows out with a pitch that is a multiple of 4 floats (117 -> 120, zeros in between) and
+    return the ``(n, 117)`` view of that buffer.  Values and shape are the same; the 16-byte row alignment is what
+    lets the first node update (``f_in``: Linear(117, H) + tanh) take the TMA-fed kernel, see :func:`node_update`."""
     assert z.is_cuda and fp.is_cuda and z.dtype == torch.uint8 and fp.dtype in (torch.float16, torch.float32)
     z, fp = z.contiguous(), fp.contiguous()
     n, n_fp = z.shape[0], (fp.shape[1] if fp.dim() == 2 else 0)
-    out = torch.empty((n, n_onehot + n_fp), device=z.device, dtype=torch.float32)
-    call("expand_atom_features", ptr(z), ptr(fp), fp.element_size(), n, n_onehot, n_fp, ptr(out), n_onehot + n_fp)
+    nf = n_onehot + n_fp
+    pitch = _pad4(nf) if pad_pitch else nf
+    base = torch.empty((n, pitch), device=z.device, dtype=torch.float32)
+    if pitch != nf:
+        base[:, nf:].zero_()
+    call("expand_atom_features", ptr(z), ptr(fp), fp.element_size(), n, n_onehot, n_fp, ptr(base), pitch)
+    if pitch == nf:
+        return base
+    out = base[:, :nf]
+    out._pb_pitch_base = base          # the zero-padded buffer this view lives in (node_update reads it)
     return out
 
 

@@ -160,7 +160,10 @@ def test_packed_entry_on_the_device_equals_the_dense_upload():
     torch.manual_seed(0)
     net = pb.Net(pb.representation.Sequential(pb.representation.dgl_legacy.gn("GraphConv"), [32, "tanh", 32, "tanh"]),
                  output_regressor_class=pb.regressors.ExactGaussianProcessRegressor).to(DEV)
-    assert torch.equal(net.representation(gd), net.representation(ref))
+    # (the packed upload lays the feature rows out with a pitch of 120 floats, so its first node update multiplies a
+    #  zero-padded matrix: the same sums, possibly by another kernel -- equal to rounding, not bit for bit)
+    assert gd.ndata["h"].stride() == (120, 1)
+    assert torch.allclose(net.representation(gd), net.representation(ref), rtol=1e-5, atol=1e-6)
     # the captured upload takes the compact tensors and yields the same graph
     src_h, dst_h, feats, y_h = e.host_tensors()
     up = pb.CapturedBatchUpload(src_h, dst_h, (feats[0], feats[1], e.n_onehot), y_h, e.num_nodes, e.batch_num_nodes,
@@ -170,6 +173,37 @@ def test_packed_entry_on_the_device_equals_the_dense_upload():
     assert torch.equal(g2.ndata["h"], ref.ndata["h"]) and torch.equal(y2.cpu(), y)
     assert up.h2d_bytes < 0.25 * (g.ndata["h"].numel() * 4)
     up.release()
+
+
+@pytest.mark.gpu
+def test_padded_pitch_features_give_the_same_first_layer():
+    """expand_atom_features(pad_pitch=True): same values, rows 16-byte aligned; node_update on the padded view (the
+    TMA-fed kernel at this size) against the dense layout (register-staged kernel), forward and weight gradients."""
+    torch.manual_seed(3)
+    n = 20000
+    z = torch.randint(0, 100, (n,), dtype=torch.uint8, device=DEV)
+    fp = torch.randint(0, 5, (n, 17), device=DEV).to(torch.float16)
+    dense = pb.ops.expand_atom_features(z, fp)
+    padded = pb.ops.expand_atom_features(z, fp, pad_pitch=True)
+    assert dense.is_contiguous() and padded.shape == dense.shape and padded.stride() == (120, 1)
+    assert torch.equal(dense, padded) and float(padded._pb_pitch_base[:, 117:].abs().max()) == 0.0
+    outs = []
+    for h in (dense, padded):
+        w = (torch.randn(128, 117, device=DEV, generator=torch.Generator(DEV).manual_seed(5)) * 0.1).requires_grad_()
+        b = torch.zeros(128, device=DEV).add_(0.01).requires_grad_()
+        y = pb.ops.node_update(h, w, b, w_is_out_in=True, act="tanh")
+        (y * torch.linspace(-1, 1, 128, device=DEV)).sum().backward()
+        outs.append((y.detach(), w.grad, b.grad))
+    for got, want in zip(outs[1], outs[0]):
+        assert got.shape == want.shape
+        assert float((got - want).norm() / want.norm()) < 2e-6, float((got - want).norm() / want.norm())
+    # (in, out) weights (GraphConv's layout) and a view that is NOT the one the expansion handed out: dense path
+    w2 = torch.randn(117, 32, device=DEV) * 0.1
+    y_a = pb.ops.node_update(padded, w2, None, w_is_out_in=False)
+    y_b = pb.ops.node_update(dense, w2, None, w_is_out_in=False)
+    assert float((y_a - y_b).norm() / y_b.norm()) < 2e-6
+    y_c = pb.ops.node_update(padded[:1000], w2, None, w_is_out_in=False)       # a slice carries no marker
+    assert float((y_c - y_b[:1000]).norm() / y_b[:1000].norm()) < 2e-6
 
 
 def test_save_and_load_round_trip(tmp_path):
